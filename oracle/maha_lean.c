@@ -1,0 +1,170 @@
+/* fp64 CPU oracle, inner loops of oracle/mahalanobis.py::MahalanobisLean.
+ *
+ * TEST INFRASTRUCTURE ONLY - never linked into libsb200.so.
+ *
+ * Restates components/outlier-detection/mahalanobis/CoreMahalanobis.py of the
+ * reference in the closed form of SURVEY.md App. A.3/A.4:
+ *   - sbo_maha_stats : L84-100  (clip, deviations from the start-of-call mean, Gram)
+ *   - sbo_maha_score : L106-136 + L147-149 (projections, warm-up gate, inverse, score)
+ * Plain scalar C, single thread, no BLAS: it is the checker, not a fast path.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define SBO_EPSILON 1e-8 /* CoreMahalanobis.py:120 */
+/* Rank guard (deliberate, documented deviation - DESIGN.md "warm-up gate"): a matrix whose smallest LU
+ * pivot is below SBO_RANK_TOL x the largest is treated as singular whatever its determinant says.  On a
+ * rank-deficient proj_cov the reference's own |det| is rounding noise (9.7e-9 against the 1e-8 threshold at
+ * d=64,k=16,row 16 of a cold start), so without the guard the opening row would be decided by noise. */
+#define SBO_RANK_TOL 1e-9
+
+static inline double clipd(double x, double lo, double hi) { return x < lo ? lo : (x > hi ? hi : x); }
+
+/* s[p] = sum_i (xc_i - m0),  G[p][p] = sum_i (xc_i - m0)(xc_i - m0)^T.  lo/hi NULL = no clipping (L85-88). */
+void sbo_maha_stats(const double* X, int64_t nb, int p, const double* lo, const double* hi, const double* m0,
+                    double* s, double* G) {
+  double* d = (double*)malloc(sizeof(double) * p);
+  memset(s, 0, sizeof(double) * p);
+  memset(G, 0, sizeof(double) * p * p);
+  for (int64_t i = 0; i < nb; ++i) {
+    const double* x = X + i * p;
+    for (int f = 0; f < p; ++f) {
+      double v = lo ? clipd(x[f], lo[f], hi[f]) : x[f];
+      d[f] = v - m0[f];
+      s[f] += d[f];
+    }
+    for (int a = 0; a < p; ++a) {
+      double da = d[a];
+      double* g = G + (size_t)a * p;
+      for (int b = a; b < p; ++b) g[b] += da * d[b];
+    }
+  }
+  for (int a = 0; a < p; ++a)
+    for (int b = 0; b < a; ++b) G[(size_t)a * p + b] = G[(size_t)b * p + a];
+  free(d);
+}
+
+/* determinant by LU with partial pivoting (what numpy.linalg.det does through getrf) */
+static double det_lu(const double* A, int k, double* w, int* full_rank) {
+  memcpy(w, A, sizeof(double) * k * k);
+  double det = 1.0, pmin = INFINITY, pmax = 0.0;
+  *full_rank = 0;
+  for (int c = 0; c < k; ++c) {
+    int piv = c;
+    double best = fabs(w[c * k + c]);
+    for (int r = c + 1; r < k; ++r)
+      if (fabs(w[r * k + c]) > best) { best = fabs(w[r * k + c]); piv = r; }
+    if (best == 0.0) return 0.0;
+    if (piv != c) {
+      for (int j = 0; j < k; ++j) { double t = w[c * k + j]; w[c * k + j] = w[piv * k + j]; w[piv * k + j] = t; }
+      det = -det;
+    }
+    double d = w[c * k + c];
+    det *= d;
+    if (fabs(d) < pmin) pmin = fabs(d);
+    if (fabs(d) > pmax) pmax = fabs(d);
+    for (int r = c + 1; r < k; ++r) {
+      double f = w[r * k + c] / d;
+      if (f != 0.0)
+        for (int j = c + 1; j < k; ++j) w[r * k + j] -= f * w[c * k + j];
+    }
+  }
+  *full_rank = pmin > SBO_RANK_TOL * pmax;
+  return det;
+}
+
+/* solve S x = u by LU with partial pivoting; returns u^T x */
+static double quad_solve(const double* S, const double* u, int k, double* w, double* x) {
+  memcpy(w, S, sizeof(double) * k * k);
+  memcpy(x, u, sizeof(double) * k);
+  for (int c = 0; c < k; ++c) {
+    int piv = c;
+    double best = fabs(w[c * k + c]);
+    for (int r = c + 1; r < k; ++r)
+      if (fabs(w[r * k + c]) > best) { best = fabs(w[r * k + c]); piv = r; }
+    if (piv != c) {
+      for (int j = 0; j < k; ++j) { double t = w[c * k + j]; w[c * k + j] = w[piv * k + j]; w[piv * k + j] = t; }
+      double t = x[c]; x[c] = x[piv]; x[piv] = t;
+    }
+    double d = w[c * k + c];
+    for (int r = c + 1; r < k; ++r) {
+      double f = w[r * k + c] / d;
+      if (f != 0.0) {
+        for (int j = c + 1; j < k; ++j) w[r * k + j] -= f * w[c * k + j];
+        x[r] -= f * x[c];
+      }
+    }
+  }
+  for (int c = k - 1; c >= 0; --c) {
+    double acc = x[c];
+    for (int j = c + 1; j < k; ++j) acc -= w[c * k + j] * x[j];
+    x[c] = acc / w[c * k + c];
+  }
+  double q = 0.0;
+  for (int c = 0; c < k; ++c) q += u[c] * x[c];
+  return q;
+}
+
+/* Rows row0 .. row0+nb-1 of one request batch.
+ *   V[p][k] top-k eigenvectors, PC0 = V^T C0 V (k x k), n = effective count (L79-82),
+ *   Z[k], Q[k][k] : in = prefix sums over the rows before row0, out = prefix after this block,
+ *   was_open : gate state before row0.  Returns the gate state after the block;
+ *   *open_at = global row index where the gate opened inside this block, else -1.
+ * score_i = (n+i-1) u^T S_i^-1 u,  S_i = (n-1) PC0 + Q_i - Z_i Z_i^T/(n+i)   (App. A.4)
+ */
+int64_t sbo_maha_score(const double* X, int64_t nb, int p, int k, const double* V, const double* m0,
+                       const double* lo, const double* hi, const double* PC0, int was_open, int64_t n,
+                       int64_t row0, double* Z, double* Q, double* score, int64_t* open_at) {
+  double* y = (double*)malloc(sizeof(double) * k * 6 + sizeof(double) * k * k * 3);
+  double* z = y + k;
+  double* u = z + k;
+  double* xs = u + k;
+  double* S = xs + 3 * k;
+  double* P = S + k * k;
+  double* w = P + k * k;
+  int is_open = was_open;
+  *open_at = -1;
+  for (int64_t r = 0; r < nb; ++r) {
+    const double* x = X + r * p;
+    int64_t i = row0 + r;
+    double ni = (double)(n + i);
+    for (int c = 0; c < k; ++c) { y[c] = 0.0; z[c] = 0.0; }
+    for (int f = 0; f < p; ++f) {
+      double raw = x[f] - m0[f];
+      double cl = (lo ? clipd(x[f], lo[f], hi[f]) : x[f]) - m0[f];
+      const double* v = V + (size_t)f * k;
+      for (int c = 0; c < k; ++c) { y[c] += raw * v[c]; z[c] += cl * v[c]; }
+    }
+    for (int a = 0; a < k; ++a)
+      for (int b = 0; b < k; ++b) {
+        double sab = (double)(n - 1) * PC0[a * k + b];
+        if (n + i > 0) sab += Q[a * k + b] - Z[a] * Z[b] / ni;
+        S[a * k + b] = sab;
+      }
+    if (!is_open) {
+      int test = 1;
+      if (i == 0) memcpy(P, PC0, sizeof(double) * k * k);
+      else if (n + i - 1 != 0) { for (int e = 0; e < k * k; ++e) P[e] = S[e] / (ni - 1.0); }
+      else test = 0;
+      if (test) {
+        int full_rank;
+        double det = det_lu(P, k, w, &full_rank);
+        if (full_rank && fabs(det) > SBO_EPSILON) { is_open = 1; *open_at = i; }
+      }
+    }
+    if (is_open) {
+      for (int c = 0; c < k; ++c) u[c] = y[c] - (n + i > 0 ? Z[c] / ni : 0.0);
+      score[r] = (ni - 1.0) * quad_solve(S, u, k, w, xs);
+    } else {
+      score[r] = 0.0;
+    }
+    for (int a = 0; a < k; ++a) {
+      Z[a] += z[a];
+      for (int b = 0; b < k; ++b) Q[a * k + b] += z[a] * z[b];
+    }
+  }
+  free(y);
+  return is_open;
+}
