@@ -1,0 +1,162 @@
+/* sb200.h - C ABI of libsb200.so: the B200-native numeric data plane behind the seldon_core component API.
+ *
+ * The reference (marcredhat/seldon-core 0.5.0-SNAPSHOT) is pure Python/Java on this path and has no FFI of
+ * its own; each entry point below names the reference function whose per-batch arithmetic it replaces
+ * (paths relative to the reference root).  INTEGRATION.md shows the ctypes stub a maintainer adds on the
+ * reference side.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative SB_ERR_* code; sb_last_error() gives the message of
+ *     the last failure on the calling thread;
+ *   - all d_* pointers are DEVICE pointers owned by the caller (e.g. torch.Tensor.data_ptr()); h_* are host
+ *     pointers; nothing is retained after the call returns except inside an opaque handle;
+ *   - `stream` is a cudaStream_t passed as uintptr_t; calls are asynchronous and stream-ordered unless stated;
+ *   - handles are not thread-safe: the Python layer serialises calls per instance (the reference wrapper
+ *     serves 10 gRPC threads, python/seldon_core/wrapper.py:132-133);
+ *   - there is no CPU fallback: without a CUDA device every compute entry point fails with SB_ERR_CUDA.
+ */
+#ifndef SB200_H
+#define SB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SB_OK 0
+#define SB_ERR_INVALID (-1)   /* bad argument (shape, null pointer, unsupported size) */
+#define SB_ERR_CUDA (-2)      /* CUDA runtime error, message in sb_last_error() */
+#define SB_ERR_WORKSPACE (-3) /* caller-provided workspace too small */
+#define SB_ERR_STATE (-4)     /* call sequence violated (e.g. pass2 before finalize) */
+
+const char* sb_last_error(void);
+int32_t sb_version(void);
+
+/* ------------------------------------------------------------------------------------------------ codec
+ * replaces python/seldon_core/utils.py:161-169 (grpc_datadef_to_array, tensor branch): the packed doubles of
+ * a serialised Tensor start `values_off` bytes into `d_wire`; they are converted to fp32 rows of `d_out`
+ * (leading dimension ld).  d_mu / d_inv_sigma (both or neither) fuse the standardise transformer
+ * (components/outlier-detection/vae/CoreVAE.py:128): out = (x - mu) * inv_sigma, inv_sigma = 1/(sigma+1e-10). */
+int32_t sb_unpack_tensor_f64(const uint8_t* d_wire, uint64_t values_off, int64_t rows, int64_t cols,
+                             const float* d_mu, const float* d_inv_sigma, float* d_out, int64_t ld,
+                             uintptr_t stream);
+
+/* replaces utils.py:174-176 (ndarray branch: MessageToDict + np.array) for a rows x cols numeric ListValue
+ * with the fixed row stride of SURVEY App. C.  *d_status (int32, device) is set non-zero if any record tag
+ * is not `0a 09 11` or a row header does not match (malformed / ragged payload). */
+int32_t sb_unpack_listvalue(const uint8_t* d_wire, uint64_t nbytes, int64_t rows, int64_t cols, float* d_out,
+                            int64_t ld, int32_t* d_status, uintptr_t stream);
+
+/* replaces utils.py:235-259 (array_to_grpc_datadef, tensor: values=array.ravel().tolist()): n values of
+ * in_dtype (SB_F32 / SB_I32) -> n little-endian doubles at d_wire_values. */
+#define SB_F32 0
+#define SB_I32 1
+int32_t sb_pack_tensor_f64(const void* d_in, int32_t in_dtype, int64_t n, uint8_t* d_wire_values, uintptr_t stream);
+
+/* replaces utils.py:281-304 (array_to_list_value).  cols == 0 encodes a 1-D list of `rows` values
+ * (the flags of CoreMahalanobis.predict).  The number of bytes written is sb_listvalue_nbytes(rows, cols). */
+int32_t sb_pack_listvalue(const void* d_in, int32_t in_dtype, int64_t rows, int64_t cols, uint8_t* d_wire,
+                          uintptr_t stream);
+uint64_t sb_listvalue_nbytes(int64_t rows, int64_t cols);
+uint64_t sb_tensor_values_offset(int64_t rows, int64_t cols);
+
+/* --------------------------------------------------------------------------------------------- combiner
+ * replaces examples/combiners/mnist_combiner/MnistCombiner.py:8-11 and the N-child rule of
+ * engine/src/main/java/io/seldon/engine/predictors/AverageCombinerUnit.java:35-79: out = (sum_j in_j) / N,
+ * summed in child order.  h_inputs is a HOST array of n_children device pointers (n_children <= 16). */
+int32_t sb_combiner_mean(const float* const* h_inputs, int32_t n_children, int64_t n_elems, float* d_out,
+                         uintptr_t stream);
+
+/* standalone standardise transformer (CoreVAE.py:128) on an fp32 device matrix. */
+int32_t sb_standardise(const float* d_in, int64_t rows, int64_t cols, int64_t ld_in, const float* d_mu,
+                       const float* d_inv_sigma, float* d_out, int64_t ld_out, uintptr_t stream);
+
+/* ------------------------------------------------------------------------------------------ mahalanobis
+ * replaces components/outlier-detection/mahalanobis/CoreMahalanobis.py.
+ * create: the constructor L26-40 (same parameters; d = number of features, fixed per handle).
+ * One request batch = pass1 -> finalize -> pass2 -> commit, which together are _get_preds (L68-151):
+ *   pass1   : L84-100  clip + additive statistics (count, sum, Gram about the start-of-call mean)
+ *   finalize: L100-112 covariance update, top-k eigenvectors (Jacobi instead of scipy eigh), projected
+ *             start-of-sub-segment inverses; with nranks > 1 the statistics of all row shards (gathered by the
+ *             caller, e.g. ncclAllGather through torch.distributed) are combined in rank order
+ *   pass2   : L106-136, L147-149 projections, warm-up gate, inverse chain, score and flag per row
+ *   commit  : L139-144 state update (mean, C, n, clip)
+ * sb_maha_batch runs the four on one GPU. */
+typedef struct sb_maha sb_maha_t;
+
+int32_t sb_maha_create(sb_maha_t** h, int32_t d, int32_t n_components, double threshold, double n_stdev,
+                       int64_t start_clip, int64_t max_n);
+int32_t sb_maha_destroy(sb_maha_t* h);
+
+/* bytes of device workspace needed for a (local) batch of up to max_rows rows */
+int32_t sb_maha_workspace_bytes(const sb_maha_t* h, int64_t max_rows, uint64_t* bytes);
+/* number of doubles in one rank's statistics record: 1 + d + d*d */
+int64_t sb_maha_stats_len(const sb_maha_t* h);
+
+int32_t sb_maha_pass1_stats(sb_maha_t* h, const float* d_X, int64_t rows, int64_t ld, void* d_ws,
+                            uint64_t ws_bytes, double* d_stats_out, uintptr_t stream);
+/* d_all_stats: nranks records of sb_maha_stats_len() doubles in rank order (NULL with nranks == 1: use this
+ * rank's own record); total_rows = rows of the whole request batch, row0 = index of this rank's first row */
+int32_t sb_maha_finalize(sb_maha_t* h, const double* d_all_stats, int32_t nranks, int32_t rank, int64_t total_rows,
+                         int64_t row0, void* d_ws, uint64_t ws_bytes, uintptr_t stream);
+int32_t sb_maha_pass2_score(sb_maha_t* h, const float* d_X, int64_t rows, int64_t ld, float* d_score,
+                            int32_t* d_flag, void* d_ws, uint64_t ws_bytes, uintptr_t stream);
+int32_t sb_maha_commit(sb_maha_t* h, uintptr_t stream);
+/* drop a batch that failed half way (state untouched) */
+int32_t sb_maha_abort_batch(sb_maha_t* h);
+
+int32_t sb_maha_batch(sb_maha_t* h, const float* d_X, int64_t rows, int64_t ld, float* d_score, int32_t* d_flag,
+                      void* d_ws, uint64_t ws_bytes, uintptr_t stream);
+
+/* Synchronising accessors (public attributes of the reference class / pickling, persistence.py:84).
+ * Any h_* pointer may be NULL.  h_C is d*d row-major; has_state = 0 while mean/C are still the scalar 0 of
+ * L35-36; has_clip = 0 while clip is None. */
+int32_t sb_maha_get_state(sb_maha_t* h, double* h_mean, double* h_C, double* h_clip_lo, double* h_clip_hi,
+                          int64_t* n, int32_t* has_state, int32_t* has_clip, uintptr_t stream);
+int32_t sb_maha_set_state(sb_maha_t* h, const double* h_mean, const double* h_C, const double* h_clip_lo,
+                          const double* h_clip_hi, int64_t n, int32_t has_state, int32_t has_clip,
+                          uintptr_t stream);
+/* sums over the last batch (metrics(), L180-192): number of flags set and sum of scores; row where the
+ * warm-up gate opened (-1: never) - diagnostics. */
+int32_t sb_maha_last_batch_sums(sb_maha_t* h, int64_t* n_flagged, double* score_sum, int64_t* gate_row,
+                                uintptr_t stream);
+/* top-k eigenvectors of the last batch, d x k row-major (diagnostics / subspace parity tests) */
+int32_t sb_maha_get_eigvecs(sb_maha_t* h, double* h_V, uintptr_t stream);
+/* tuning knobs: SB_OPT_GRAM_TERMS 1|3 (TF32 products per Gram element, default 3),
+ * SB_OPT_FORCE_GENERIC 0|1 (skip the d=64 tensor-core kernels) */
+#define SB_OPT_GRAM_TERMS 1
+#define SB_OPT_FORCE_GENERIC 2
+int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t value);
+/* number of kernel launches issued through this handle so far (bench.py's gpu_launches) */
+int64_t sb_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------- routers
+ * replaces components/routers/epsilon-greedy/EpsilonGreedy.py (kind 0) and
+ * components/routers/thompson-sampling/ThompsonSampling.py (kind 1), batched: T interleaved
+ * route()/send_feedback() calls in one launch, decisions bit-identical to the reference under a seed.
+ * create = __init__ (L35-85 / L35-76): seed > 0 seeds both MT19937 streams like random.seed/np.random.seed;
+ * best_branch <= 0 draws the start branch like random.choice(range(n)). */
+typedef struct sb_router sb_router_t;
+#define SB_ROUTER_EPSILON_GREEDY 0
+#define SB_ROUTER_THOMPSON 1
+#define SB_REWARD_PER_CALL 0  /* d_reward[t]                                  */
+#define SB_REWARD_TABLE 1     /* d_reward[t*n_branches + arm]                  */
+#define SB_REWARD_BERNOULLI 2 /* d_reward[t] = u_t; reward = u_t < d_arm_p[arm] */
+int32_t sb_router_create(sb_router_t** h, int32_t kind, int32_t n_branches, double epsilon, int64_t seed,
+                         int32_t best_branch);
+int32_t sb_router_destroy(sb_router_t* h);
+/* d_rows_per_call may be NULL (1 row per call).  route only: reward_mode = -1 (no feedback applied). */
+int32_t sb_router_run(sb_router_t* h, int64_t T, const int64_t* d_rows_per_call, const float* d_reward,
+                      const float* d_arm_p, int32_t reward_mode, int32_t* d_decisions, uintptr_t stream);
+/* single feedback for an externally chosen arm (send_feedback of the class API) */
+int32_t sb_router_feedback(sb_router_t* h, int32_t arm, int64_t rows, double reward, uintptr_t stream);
+/* state blob for pickling: success[n], tries[n], best_branch, then both generator states.  Synchronises. */
+int64_t sb_router_state_len(const sb_router_t* h);
+int32_t sb_router_get_state(sb_router_t* h, int64_t* h_state, uintptr_t stream);
+int32_t sb_router_set_state(sb_router_t* h, const int64_t* h_state, uintptr_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SB200_H */

@@ -1,0 +1,170 @@
+"""SeldonMessage numeric payloads <-> device tensors.
+
+Host-side mirror of the numeric branches of ``python/seldon_core/utils.py``: ``grpc_datadef_to_array`` (L147-181),
+``array_to_grpc_datadef`` / ``array_to_list_value`` (L235-304) and the naming rule of ``client_class_names``
+(``python/seldon_core/user_model.py:103-131``).  Only the small varint headers are handled on the host; the bulk
+(the packed doubles / the 11-byte ListValue records) is converted by libsb200.so on the GPU.
+"""
+import numpy as np
+
+from . import _cabi
+from .errors import SeldonB200Error
+
+
+def _varint(n):
+    out = bytearray()
+    while True:
+        b = n & 0x7F
+        n >>= 7
+        if n:
+            out.append(b | 0x80)
+        else:
+            out.append(b)
+            return bytes(out)
+
+
+def _read_varint(buf, pos):
+    shift = val = 0
+    while True:
+        b = buf[pos]
+        pos += 1
+        val |= (b & 0x7F) << shift
+        if not b & 0x80:
+            return val, pos
+        shift += 7
+
+
+def _device(device):
+    import torch
+
+    if not torch.cuda.is_available():
+        raise SeldonB200Error("no CUDA device: seldon_core_b200 has no CPU fallback", status_code=500)
+    return torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+
+
+def _upload(wire, dev, offset_to_align):
+    """Copy wire bytes to the device so that byte `offset_to_align` lands on a 16-byte boundary."""
+    import torch
+
+    pad = (-offset_to_align) % 16
+    host = torch.empty(pad + len(wire), dtype=torch.uint8).pin_memory()
+    host[pad:] = torch.frombuffer(memoryview(wire), dtype=torch.uint8)
+    return host.to(dev, non_blocking=True), pad
+
+
+def parse_tensor_header(wire):
+    """Shape and offset of the packed doubles of a serialised Tensor (proto/prediction.proto:33-38)."""
+    pos, shape = 0, []
+    if wire[:1] == b"\x0a":
+        n, pos = _read_varint(wire, 1)
+        end = pos + n
+        while pos < end:
+            v, pos = _read_varint(wire, pos)
+            shape.append(v)
+    count = int(np.prod(shape)) if shape else 0
+    return shape, len(wire) - 8 * count  # utils.py:164-169: the values are the tail of the message
+
+
+def decode_tensor(wire, device=None, mu=None, inv_sigma=None):
+    """Serialised Tensor -> CUDA float32 (rows, cols); optional fused standardise (device float32 vectors)."""
+    import torch
+
+    dev = _device(device)
+    shape, off = parse_tensor_header(wire)
+    if len(shape) != 2:
+        raise SeldonB200Error("tensor payload must be 2-D, got shape %s" % (shape,))
+    rows, cols = shape
+    buf, pad = _upload(wire, dev, off)
+    out = torch.empty((rows, cols), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _cabi.check(_cabi.lib().sb_unpack_tensor_f64(buf.data_ptr(), pad + off, rows, cols,
+                                                     None if mu is None else mu.data_ptr(),
+                                                     None if inv_sigma is None else inv_sigma.data_ptr(),
+                                                     out.data_ptr(), cols, torch.cuda.current_stream().cuda_stream))
+    return out
+
+
+def decode_ndarray(wire, cols, device=None):
+    """Serialised 2-D numeric ListValue -> CUDA float32 (rows, cols).  `cols` comes from the first row header or
+    from the request's `names`; a ragged or non-numeric payload raises."""
+    import torch
+
+    dev = _device(device)
+    L = _cabi.lib()
+    row_bytes = L.sb_listvalue_nbytes(1, cols)
+    if row_bytes == 0 or len(wire) % row_bytes:
+        raise SeldonB200Error("ndarray payload of %d bytes is not a whole number of %d-column rows" % (len(wire), cols))
+    rows = len(wire) // row_bytes
+    buf, pad = _upload(wire, dev, 0)
+    out = torch.empty((rows, cols), dtype=torch.float32, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _cabi.check(L.sb_unpack_listvalue(buf.data_ptr() + pad, len(wire), rows, cols, out.data_ptr(), cols,
+                                          status.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    if int(status.item()) != 0:
+        raise SeldonB200Error("malformed ndarray payload (not a rows x %d list of numbers)" % cols)
+    return out
+
+
+def ndarray_cols(wire):
+    """Number of columns announced by the first row header of a 2-D ListValue."""
+    if wire[:1] != b"\x0a":
+        raise SeldonB200Error("not a ListValue")
+    _, pos = _read_varint(wire, 1)
+    if wire[pos:pos + 1] != b"\x32":
+        raise SeldonB200Error("not a 2-D ListValue")
+    l2, _ = _read_varint(wire, pos + 1)
+    if l2 % 11:
+        raise SeldonB200Error("not a numeric ListValue")
+    return l2 // 11
+
+
+def _dtype_code(t):
+    import torch
+
+    if t.dtype == torch.float32:
+        return _cabi.SB_F32
+    if t.dtype == torch.int32:
+        return _cabi.SB_I32
+    raise SeldonB200Error("encode expects float32 or int32 device tensors")
+
+
+def encode_tensor(t):
+    """CUDA float32/int32 tensor -> bytes of Tensor(shape, values) (utils.py:255-259)."""
+    import torch
+
+    t = t.contiguous()
+    shape = b"".join(_varint(int(s)) for s in t.shape)
+    head = b"\x0a" + _varint(len(shape)) + shape + b"\x12" + _varint(8 * t.numel())
+    vals = torch.empty(8 * t.numel(), dtype=torch.uint8, device=t.device)
+    with torch.cuda.device(t.device):
+        _cabi.check(_cabi.lib().sb_pack_tensor_f64(t.data_ptr(), _dtype_code(t), t.numel(), vals.data_ptr(),
+                                                   torch.cuda.current_stream().cuda_stream))
+    return head + vals.cpu().numpy().tobytes()
+
+
+def encode_ndarray(t):
+    """CUDA float32/int32 tensor (1-D or 2-D) -> bytes of the ListValue of array_to_list_value (utils.py:281-304)."""
+    import torch
+
+    t = t.contiguous()
+    if t.dim() == 1:
+        rows, cols = t.shape[0], 0
+    elif t.dim() == 2:
+        rows, cols = t.shape
+    else:
+        raise SeldonB200Error("encode_ndarray supports 1-D and 2-D tensors")
+    L = _cabi.lib()
+    nbytes = L.sb_listvalue_nbytes(rows, cols)
+    out = torch.empty(int(nbytes), dtype=torch.uint8, device=t.device)
+    with torch.cuda.device(t.device):
+        _cabi.check(L.sb_pack_listvalue(t.data_ptr(), _dtype_code(t), rows, cols, out.data_ptr(),
+                                        torch.cuda.current_stream().cuda_stream))
+    return out.cpu().numpy().tobytes()
+
+
+def class_names(result_ndim, n_targets, user_names=None):
+    """user_model.py:117-131."""
+    if result_ndim > 1:
+        return list(user_names) if user_names is not None else ["t:{}".format(i) for i in range(n_targets)]
+    return []

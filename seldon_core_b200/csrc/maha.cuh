@@ -1,0 +1,87 @@
+// Internal declarations shared by the Mahalanobis translation units.
+#pragma once
+#include "common.cuh"
+
+struct sb_maha;
+
+namespace sb {
+
+// A request batch (the rows this rank holds) is cut into contiguous sub-segments.  Pass 1 emits one
+// (row-sum, Gram) partial per sub-segment; after the eigenvectors are known their projections are
+// prefix-summed so that pass 2 can start an independent inverse chain at every sub-segment
+// (SURVEY App. A.4).  The first `nshort` sub-segments are short: a cold start spends them in the exact
+// fp64 warm-up kernel.
+struct SubLayout {
+  int64_t rows;
+  int64_t sublen;
+  int32_t nshort;
+  int32_t shortlen;
+  int32_t nsub;
+};
+
+__host__ __device__ inline int64_t sub_begin(const SubLayout& L, int s) {
+  int64_t b = s < L.nshort ? (int64_t)s * L.shortlen : (int64_t)L.nshort * L.shortlen + (int64_t)(s - L.nshort) * L.sublen;
+  return b < L.rows ? b : L.rows;
+}
+
+constexpr int kTargetChains = kNumSMs * 16;  // independent inverse chains wanted in flight
+constexpr int kShortLen = 128;
+constexpr int kMinSubLen = 64;
+constexpr int kMaxSubLen = 4096;  // bounds the fp32 drift of a Sherman-Morrison chain
+constexpr int kMaxD = 512;
+constexpr int kMaxKP = 32;
+
+SubLayout make_layout(int64_t rows);
+int64_t max_subsegments(int64_t max_rows);
+
+constexpr int SUBFLAG_OPEN = 1;  // warm-up gate test passes at the first row of the sub-segment
+constexpr int SUBFLAG_WELL = 2;  // start matrix well enough conditioned for the fp32 chain
+
+struct MahaWs {  // device pointers carved out of the caller's workspace
+  float* partials;     // [nsub][d + d*d]
+  double* subproj;     // [nsub + 1][KP + KP*KP]   (+1: totals after the scan)
+  float* sub_P;        // [nsub][KP*KP]  inverse of S at the sub-segment start
+  float* sub_Z;        // [nsub][KP]     prefix of projected deviations at the start
+  int32_t* sub_flags;  // [nsub]
+  double* stats;       // [1 + d + d*d]  this rank's totals
+  double* rank_pre;    // [1 + d + d*d]  totals of the ranks before this one
+  double* rank_proj;   // [KP + KP*KP]   their projection (offset of every prefix on this rank)
+  double* eig_W;       // [d*d] Jacobi work
+  double* eig_V;       // [d*d]
+  uint64_t bytes;
+};
+
+int launch_pass1(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws, cudaStream_t st);
+int launch_reduce(const sb_maha* h, const MahaWs& ws, double* stats_out, cudaStream_t st);
+int launch_finalize_cov(sb_maha* h, const double* all_stats, int nranks, int rank, const MahaWs& ws, cudaStream_t st);
+int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st);
+int launch_prefix(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream_t st);
+int launch_score(sb_maha* h, const float* X, int64_t ld, float* score, int32_t* flag, const MahaWs& ws,
+                 cudaStream_t st);
+
+}  // namespace sb
+
+struct sb_maha {
+  int d, k, KP;
+  double threshold, n_stdev;
+  int64_t start_clip, max_n;
+  // host-side mirror of the scalar state
+  int64_t n;
+  int has_state, has_clip;
+  // batch in flight
+  int stage;  // 0 idle, 1 pass1 done, 2 finalized, 3 scored
+  int64_t rows_local, rows_total, row0, n_eff;
+  int use_clip;
+  sb::SubLayout lay;
+  // options
+  int gram_terms, force_generic;
+  // device state
+  double *d_mean, *d_C, *d_lo, *d_hi;      // committed
+  double *d_mean1, *d_C1, *d_lo1, *d_hi1;  // pending (this batch)
+  float *d_mean_f, *d_lo_f, *d_hi_f;       // fp32 copies of the committed state
+  double *d_V, *d_PC0;                     // [d][KP], [KP][KP]
+  float* d_Vf;
+  double* d_evals;                 // [KP]
+  long long* d_gate;               // [0] b*, [1] i* (global row), [2] n_flagged, [3] eigh sweeps, [4] total rows
+  double* d_score_sum;             // [1]
+};

@@ -1,0 +1,134 @@
+// Top-k eigenvectors of the d x d covariance by one-sided (Hestenes) Jacobi in fp64.
+//
+// Replaces the scipy.linalg.eigh(cov_batch, eigvals=(p-k, p-1)) call of CoreMahalanobis.py:103 (LAPACK, a
+// third-party dependency of the reference).  Only the span of the k leading eigenvectors enters the scores
+// (they are invariant to the basis of that subspace), so the solver is free to return any
+// orthonormal basis; parity is tested on the projector V V^T.
+//
+// One CTA, 32 warps.  W starts as C (columns), V as I; a rotation of columns (p,q) that makes W_p and W_q
+// orthogonal is applied to both.  At convergence W = C V has orthogonal columns, i.e. V diagonalises C^2 and
+// hence C, with |lambda_j| = ||W_j||.  Per step the d/2 disjoint pairs of a round-robin tournament are rotated
+// in parallel, one warp per pair, dot products by warp shuffles.  For 2*d*d*8 B <= 200 KB both matrices live
+// in shared memory (d <= 111), otherwise in the (L2-resident) workspace.  This is a latency kernel
+// (about 4*d^3 flops per sweep), not a roofline kernel; bench.py reports its time.
+#include "maha.cuh"
+
+namespace sb {
+namespace {
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <bool SMEM>
+__global__ void __launch_bounds__(1024, 1)
+jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, double* gV, double* __restrict__ Vd,
+            float* __restrict__ Vf, double* __restrict__ evals, long long* __restrict__ gate) {
+  extern __shared__ double sm[];
+  double* W = SMEM ? sm : gW;
+  double* V = SMEM ? sm + (size_t)d * d : gV;
+  __shared__ int rotated;
+  __shared__ double norms[kMaxD];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+
+  for (int idx = tid; idx < d * d; idx += blockDim.x) {
+    int c = idx / d, r = idx - c * d;
+    W[idx] = C[(size_t)r * d + c];  // column c of C (C is symmetric; kept explicit)
+    V[idx] = r == c ? 1.0 : 0.0;
+  }
+  const int m = (d + 1) & ~1;  // players in the tournament (one bye if d is odd)
+  int sweeps = 0;
+  for (; sweeps < 40; ++sweeps) {
+    __syncthreads();
+    if (tid == 0) rotated = 0;
+    __syncthreads();
+    for (int step = 0; step < m - 1; ++step) {
+      for (int pr = warp; pr < m / 2; pr += nwarp) {
+        int p = pr == 0 ? m - 1 : (step + pr) % (m - 1);
+        int q = (step + m - 1 - pr) % (m - 1);
+        if (p >= d || q >= d) continue;
+        if (p > q) { int tmp = p; p = q; q = tmp; }
+        double* wp = W + (size_t)p * d;
+        double* wq = W + (size_t)q * d;
+        double al = 0.0, be = 0.0, ga = 0.0;
+        for (int r = lane; r < d; r += 32) {
+          double a = wp[r], b = wq[r];
+          al = fma(a, a, al);
+          be = fma(b, b, be);
+          ga = fma(a, b, ga);
+        }
+        al = warp_sum(al); be = warp_sum(be); ga = warp_sum(ga);
+        if (al == 0.0 || be == 0.0) continue;
+        if (fabs(ga) <= 1e-15 * sqrt(al * be)) continue;
+        const double zeta = (be - al) / (2.0 * ga);
+        const double tt = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+        const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
+        double* vp = V + (size_t)p * d;
+        double* vq = V + (size_t)q * d;
+        for (int r = lane; r < d; r += 32) {
+          double a = wp[r], b = wq[r];
+          wp[r] = cs * a - sn * b;
+          wq[r] = sn * a + cs * b;
+          a = vp[r]; b = vq[r];
+          vp[r] = cs * a - sn * b;
+          vq[r] = sn * a + cs * b;
+        }
+        if (lane == 0) rotated = 1;
+      }
+      __syncthreads();
+    }
+    if (!rotated) break;
+  }
+  __syncthreads();
+  // |lambda_j| = ||W_j||; rank the columns and emit the k largest (descending), zero-padded to KP columns
+  for (int c = warp; c < d; c += nwarp) {
+    double a = 0.0;
+    for (int r = lane; r < d; r += 32) a = fma(W[(size_t)c * d + r], W[(size_t)c * d + r], a);
+    a = warp_sum(a);
+    if (lane == 0) norms[c] = sqrt(a);
+  }
+  __syncthreads();
+  for (int idx = tid; idx < d * KP; idx += blockDim.x) {
+    int f = idx / KP, c = idx - f * KP;
+    if (c >= k) { Vd[idx] = 0.0; Vf[idx] = 0.f; }
+  }
+  for (int c = tid; c < d; c += blockDim.x) {
+    int rank = 0;
+    const double nc = norms[c];
+    for (int o = 0; o < d; ++o) rank += (norms[o] > nc) || (norms[o] == nc && o < c);
+    if (rank < k) {
+      evals[rank] = nc;
+      for (int f = 0; f < d; ++f) {
+        double v = V[(size_t)c * d + f];
+        Vd[(size_t)f * KP + rank] = v;
+        Vf[(size_t)f * KP + rank] = (float)v;
+      }
+    }
+  }
+  if (tid == 0) gate[3] = sweeps;
+}
+
+}  // namespace
+
+int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
+  const int d = h->d;
+  const size_t need = 2 * (size_t)d * d * sizeof(double);
+  if (need <= 200 * 1024) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      SB_CUDA(cudaFuncSetAttribute(jacobi_topk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      attr_set = true;
+    }
+    jacobi_topk<true><<<1, 1024, need, st>>>(h->d_C1, d, h->k, h->KP, nullptr, nullptr, h->d_V, h->d_Vf, h->d_evals,
+                                            h->d_gate);
+  } else {
+    jacobi_topk<false><<<1, 1024, 0, st>>>(h->d_C1, d, h->k, h->KP, ws.eig_W, ws.eig_V, h->d_V, h->d_Vf, h->d_evals,
+                                           h->d_gate);
+  }
+  SB_LAUNCH_CHECK();
+  return SB_OK;
+}
+
+}  // namespace sb

@@ -1,0 +1,370 @@
+// Mahalanobis pass 1: clip + additive statistics, and the covariance update.
+//
+// Replaces CoreMahalanobis.py:84-100 of the reference (clip, running mean, the (nb,p,p) outer-product tensor
+// and its sum) through the Gram identity of SURVEY App. A.2: with a = the start-of-call mean,
+//     s = sum_i (xc_i - a),   G = sum_i (xc_i - a)(xc_i - a)^T
+// are additive over rows, so every sub-segment of the batch produces one partial (s, G) and
+//     sum_i B_i = G - s s^T/nb + n nb/(n+nb) dd^T,  d = s/nb          (L98-99)
+//     C1 = (n-1)/den C0 + sum_i B_i / den,  den = n + max(1, nb-1)    (L100)
+//     mean1 = a + nb/(n+nb) d                                         (L93 at i = nb-1)
+//
+// Kernels
+//   pass1_gram64_tf32 : d = 64.  One warp per sub-segment streams 8 rows (2 KB) per step straight from HBM
+//                       into mma.sync m16n8k8 TF32 fragments (A and B fragments are the same registers because
+//                       the Gram is X^T X), 3xTF32 split for fp32-level products, fp32 accumulation, upper
+//                       triangle only (20 of 32 tiles).  Algorithmic traffic 4*d B/row; HBM-bound at d = 64.
+//   pass1_generic     : any d <= 512, exact fp32 FMA, 4x4 register tiles out of shared memory.
+//   reduce_partials   : fp64 sum over sub-segments -> this rank's statistics record.
+//   finalize_cov      : combines the records of all ranks in rank order, forms C1, mean1, clip1.
+#include "maha.cuh"
+
+namespace sb {
+
+SubLayout make_layout(int64_t rows) {
+  SubLayout L{};
+  L.rows = rows;
+  L.shortlen = kShortLen;
+  L.nshort = rows >= 8 * kShortLen ? 2 : 0;
+  int64_t rest = rows - (int64_t)L.nshort * L.shortlen;
+  if (rest <= 0) {
+    L.sublen = kMinSubLen;
+    L.nsub = L.nshort;
+    return L;
+  }
+  int64_t m = ceil_div(rest, (int64_t)kTargetChains * kMaxSubLen);
+  int64_t len = ceil_div(rest, (int64_t)kTargetChains * m);
+  len = ceil_div(len, 16) * 16;
+  if (len < kMinSubLen) len = kMinSubLen;
+  L.sublen = len;
+  L.nsub = L.nshort + (int32_t)ceil_div(rest, len);
+  return L;
+}
+
+int64_t max_subsegments(int64_t max_rows) {
+  // make_layout never produces more than kTargetChains*m + nshort sub-segments, m as computed for max_rows
+  int64_t m = ceil_div(max_rows > 0 ? max_rows : 1, (int64_t)kTargetChains * kMaxSubLen);
+  int64_t a = (int64_t)kTargetChains * m + 4;
+  int64_t b = ceil_div(max_rows, kMinSubLen) + 4;
+  return a < b ? a : b;
+}
+
+namespace {
+
+// ---------------------------------------------------------------------------------------- d = 64, tensor cores
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void mma_m16n8k8_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                                 uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// Logical feature L = g + 8*jj (g = lane/4, jj = 0..7) is physical column phys64(L): each lane loads two float4
+// per row (columns 4g..4g+3 and 32+4g..32+4g+3), so a warp instruction covers 128 contiguous bytes of each of 4 rows.
+__device__ __forceinline__ int phys64(int L) {
+  int g = L & 7, jj = L >> 3;
+  return jj < 4 ? 4 * g + jj : 32 + 4 * g + (jj - 4);
+}
+
+template <bool CLIP, int TERMS>
+__global__ void __launch_bounds__(256, 1)
+pass1_gram64_tf32(const float* __restrict__ X, int64_t ld, SubLayout lay, const float* __restrict__ mean_f,
+                  const float* __restrict__ lo_f, const float* __restrict__ hi_f, float* __restrict__ partials) {
+  constexpr int D = 64, PS = D + D * D;
+  const int lane = threadIdx.x & 31;
+  const int g = lane >> 2, t = lane & 3;
+  const int warps_total = gridDim.x * (blockDim.x >> 5);
+  const int gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+
+  // per-lane constants for its 8 physical columns
+  float m[8], lo[8], hi[8];
+#pragma unroll
+  for (int jj = 0; jj < 8; ++jj) {
+    int col = (jj < 4 ? 4 * g + jj : 32 + 4 * g + (jj - 4));
+    m[jj] = mean_f[col];
+    if (CLIP) { lo[jj] = lo_f[col]; hi[jj] = hi_f[col]; }
+  }
+
+  for (int sub = gw; sub < lay.nsub; sub += warps_total) {
+    const int64_t r0 = sub_begin(lay, sub), r1 = sub_begin(lay, sub + 1);
+    float acc[4][8][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[i][j][e] = 0.f;
+    float ssum[8];
+#pragma unroll
+    for (int jj = 0; jj < 8; ++jj) ssum[jj] = 0.f;
+
+    float4 nxt[4];
+    auto load_chunk = [&](int64_t r, float4 (&v)[4]) {
+      const int64_t ra = r + t, rb = r + t + 4;
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4* pa = reinterpret_cast<const float4*>(X + ra * ld);
+      const float4* pb = reinterpret_cast<const float4*>(X + rb * ld);
+      v[0] = ra < r1 ? ldg_stream_f4(pa + g) : z;
+      v[1] = ra < r1 ? ldg_stream_f4(pa + 8 + g) : z;
+      v[2] = rb < r1 ? ldg_stream_f4(pb + g) : z;
+      v[3] = rb < r1 ? ldg_stream_f4(pb + 8 + g) : z;
+    };
+    if (r0 < r1) load_chunk(r0, nxt);
+    for (int64_t r = r0; r < r1; r += 8) {
+      float x[2][8];
+      x[0][0] = nxt[0].x; x[0][1] = nxt[0].y; x[0][2] = nxt[0].z; x[0][3] = nxt[0].w;
+      x[0][4] = nxt[1].x; x[0][5] = nxt[1].y; x[0][6] = nxt[1].z; x[0][7] = nxt[1].w;
+      x[1][0] = nxt[2].x; x[1][1] = nxt[2].y; x[1][2] = nxt[2].z; x[1][3] = nxt[2].w;
+      x[1][4] = nxt[3].x; x[1][5] = nxt[3].y; x[1][6] = nxt[3].z; x[1][7] = nxt[3].w;
+      const bool va = (r + t) < r1, vb = (r + t + 4) < r1;
+      if (r + 8 < r1) load_chunk(r + 8, nxt);
+
+      uint32_t big[2][8], sml[2][8];
+#pragma unroll
+      for (int rr = 0; rr < 2; ++rr) {
+        const bool valid = rr == 0 ? va : vb;
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj) {
+          float v = x[rr][jj];
+          if (CLIP) v = fminf(fmaxf(v, lo[jj]), hi[jj]);
+          v = valid ? v - m[jj] : 0.f;
+          ssum[jj] += v;
+          big[rr][jj] = to_tf32(v);
+          if (TERMS == 3) sml[rr][jj] = to_tf32(v - __uint_as_float(big[rr][jj]));
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if (j >= 2 * i) {
+            if (TERMS == 3) {
+              mma_m16n8k8_tf32(acc[i][j], sml[0][2 * i], sml[0][2 * i + 1], sml[1][2 * i], sml[1][2 * i + 1],
+                               big[0][j], big[1][j]);
+              mma_m16n8k8_tf32(acc[i][j], big[0][2 * i], big[0][2 * i + 1], big[1][2 * i], big[1][2 * i + 1],
+                               sml[0][j], sml[1][j]);
+            }
+            mma_m16n8k8_tf32(acc[i][j], big[0][2 * i], big[0][2 * i + 1], big[1][2 * i], big[1][2 * i + 1],
+                             big[0][j], big[1][j]);
+          }
+        }
+      }
+    }
+
+    // write the partial: s, then G (logical upper triangle mirrored to both halves)
+    float* part = partials + (size_t)sub * PS;
+#pragma unroll
+    for (int jj = 0; jj < 8; ++jj) {
+      float v = ssum[jj];
+      v += __shfl_xor_sync(0xffffffffu, v, 1);
+      v += __shfl_xor_sync(0xffffffffu, v, 2);
+      if (t == 0) part[jj < 4 ? 4 * g + jj : 32 + 4 * g + (jj - 4)] = v;
+    }
+    float* G = part + D;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (j >= 2 * i) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int Lm = 16 * i + g + ((e & 2) ? 8 : 0);
+            const int Ln = 8 * j + 2 * t + (e & 1);
+            if (Lm <= Ln) {
+              const int pm = phys64(Lm), pn = phys64(Ln);
+              G[pm * D + pn] = acc[i][j][e];
+              G[pn * D + pm] = acc[i][j][e];
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+// --------------------------------------------------------------------------------------------- generic, fp32
+constexpr int kGenRows = 16;
+
+template <bool CLIP>
+__global__ void __launch_bounds__(256)
+pass1_generic(const float* __restrict__ X, int64_t ld, int d, SubLayout lay, const float* __restrict__ mean_f,
+              const float* __restrict__ lo_f, const float* __restrict__ hi_f, float* __restrict__ partials) {
+  extern __shared__ float xs[];  // [kGenRows][dp]
+  const int dp = (d + 3) & ~3;
+  const int T4 = dp >> 2;
+  const size_t PS = (size_t)d + (size_t)d * d;
+  for (int sub = blockIdx.x; sub < lay.nsub; sub += gridDim.x) {
+    const int64_t r0 = sub_begin(lay, sub), r1 = sub_begin(lay, sub + 1);
+    float* part = partials + (size_t)sub * PS;
+    bool first = true;
+    for (int64_t r = r0; r < r1 || first; r += kGenRows) {
+      __syncthreads();
+      for (int idx = threadIdx.x; idx < kGenRows * dp; idx += blockDim.x) {
+        int rr = idx / dp, f = idx - rr * dp;
+        float v = 0.f;
+        if (f < d && r + rr < r1) {
+          v = X[(r + rr) * ld + f];
+          if (CLIP) v = fminf(fmaxf(v, lo_f[f]), hi_f[f]);
+          v -= mean_f[f];
+        }
+        xs[idx] = v;
+      }
+      __syncthreads();
+      for (int f = threadIdx.x; f < d; f += blockDim.x) {
+        float a = 0.f;
+#pragma unroll
+        for (int rr = 0; rr < kGenRows; ++rr) a += xs[rr * dp + f];
+        part[f] = first ? a : part[f] + a;
+      }
+      for (int tile = threadIdx.x; tile < T4 * T4; tile += blockDim.x) {
+        const int ta = tile / T4, tb = tile - ta * T4;
+        if (ta > tb) continue;
+        float acc[4][4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+#pragma unroll 4
+        for (int rr = 0; rr < kGenRows; ++rr) {
+          const float4 va = *reinterpret_cast<const float4*>(xs + rr * dp + 4 * ta);
+          const float4 vb = *reinterpret_cast<const float4*>(xs + rr * dp + 4 * tb);
+          const float a4[4] = {va.x, va.y, va.z, va.w}, b4[4] = {vb.x, vb.y, vb.z, vb.w};
+#pragma unroll
+          for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(a4[a], b4[b], acc[a][b]);
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) {
+            const int fa = 4 * ta + a, fb = 4 * tb + b;
+            if (fa < d && fb < d && fa <= fb) {
+              float* p = part + d + (size_t)fa * d + fb;
+              *p = first ? acc[a][b] : *p + acc[a][b];
+            }
+          }
+      }
+      first = false;
+    }
+  }
+}
+
+// stats[0] = rows, stats[1..d] = s, stats[1+d ..] = G (full, symmetric).  Partials hold G's upper triangle.
+__global__ void __launch_bounds__(256)
+reduce_partials(const float* __restrict__ partials, int nsub, int d, int64_t rows, double* __restrict__ stats) {
+  const size_t PS = (size_t)d + (size_t)d * d;
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e == 0) stats[0] = (double)rows;
+  if (e >= PS) return;
+  size_t src = e;
+  if (e >= (size_t)d) {
+    size_t a = (e - d) / d, b = (e - d) - a * d;
+    if (a > b) src = d + b * d + a;
+  }
+  double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
+  int s = 0;
+  for (; s + 3 < nsub; s += 4) {
+    acc0 += (double)partials[(size_t)s * PS + src];
+    acc1 += (double)partials[(size_t)(s + 1) * PS + src];
+    acc2 += (double)partials[(size_t)(s + 2) * PS + src];
+    acc3 += (double)partials[(size_t)(s + 3) * PS + src];
+  }
+  for (; s < nsub; ++s) acc0 += (double)partials[(size_t)s * PS + src];
+  stats[1 + e] = (acc0 + acc1) + (acc2 + acc3);
+}
+
+// One thread per covariance element.  all_stats: [nranks][1 + d + d*d].
+__global__ void __launch_bounds__(256)
+finalize_cov(const double* __restrict__ all_stats, int nranks, int rank, int d, long long n_eff, long long n_new_total,
+             long long start_clip, double n_stdev, const double* __restrict__ mean0, const double* __restrict__ C0,
+             double* __restrict__ mean1, double* __restrict__ C1, double* __restrict__ lo1, double* __restrict__ hi1,
+             double* __restrict__ rank_pre, long long* __restrict__ gate) {
+  const size_t SL = 1 + (size_t)d + (size_t)d * d;
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // index into the d*d part
+  if (e >= (size_t)d * d) return;
+  const int a = (int)(e / d), b = (int)(e - (size_t)a * d);
+  double nb = 0.0, sa = 0.0, sb_ = 0.0, gab = 0.0, pre_g = 0.0, pre_cnt = 0.0, pre_sb = 0.0;
+  for (int r = 0; r < nranks; ++r) {
+    const double* st = all_stats + (size_t)r * SL;
+    if (r == rank) { pre_g = gab; pre_cnt = nb; pre_sb = sb_; }
+    nb += st[0];
+    sa += st[1 + a];
+    sb_ += st[1 + b];
+    gab += st[1 + d + e];
+  }
+  rank_pre[1 + d + e] = pre_g;
+  if (a == 0) rank_pre[1 + b] = pre_sb;
+  if (e == 0) { rank_pre[0] = pre_cnt; gate[4] = (long long)(nb + 0.5); }
+  const double n = (double)n_eff;
+  const double da = sa / nb, db = sb_ / nb;
+  double sumB = gab - sa * sb_ / nb;
+  if (n + nb > 0.0) sumB += n * nb / (n + nb) * da * db;
+  const double den = n + fmax(1.0, nb - 1.0);
+  const double c1 = (n - 1.0) / den * C0[e] + sumB / den;
+  C1[e] = c1;
+  if (a == b) {
+    const double m1 = mean0[a] + nb / (n + nb) * da;
+    mean1[a] = m1;
+    if (n_new_total > start_clip) {
+      const double sd = sqrt(c1);
+      lo1[a] = m1 - n_stdev * sd;
+      hi1[a] = m1 + n_stdev * sd;
+    }
+  }
+}
+
+}  // namespace
+
+int launch_pass1(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws, cudaStream_t st) {
+  const SubLayout& L = h->lay;
+  if (L.nsub == 0) return SB_OK;
+  const bool fast = h->d == 64 && !h->force_generic && (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
+  if (fast) {
+    int grid = (int)ceil_div(L.nsub, 8);
+    if (grid > kNumSMs) grid = kNumSMs;
+    if (h->use_clip) {
+      if (h->gram_terms == 3)
+        pass1_gram64_tf32<true, 3><<<grid, 256, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials);
+      else
+        pass1_gram64_tf32<true, 1><<<grid, 256, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials);
+    } else {
+      if (h->gram_terms == 3)
+        pass1_gram64_tf32<false, 3><<<grid, 256, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials);
+      else
+        pass1_gram64_tf32<false, 1><<<grid, 256, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials);
+    }
+  } else {
+    int grid = L.nsub < kNumSMs * 4 ? L.nsub : kNumSMs * 4;
+    size_t smem = (size_t)kGenRows * ((h->d + 3) & ~3) * sizeof(float);
+    if (h->use_clip)
+      pass1_generic<true><<<grid, 256, smem, st>>>(X, ld, h->d, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials);
+    else
+      pass1_generic<false><<<grid, 256, smem, st>>>(X, ld, h->d, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials);
+  }
+  SB_LAUNCH_CHECK();
+  return SB_OK;
+}
+
+int launch_reduce(const sb_maha* h, const MahaWs& ws, double* stats_out, cudaStream_t st) {
+  const size_t PS = (size_t)h->d + (size_t)h->d * h->d;
+  reduce_partials<<<(int)ceil_div(PS, 256), 256, 0, st>>>(ws.partials, h->lay.nsub, h->d, h->rows_local, stats_out);
+  SB_LAUNCH_CHECK();
+  return SB_OK;
+}
+
+int launch_finalize_cov(sb_maha* h, const double* all_stats, int nranks, int rank, const MahaWs& ws, cudaStream_t st) {
+  const int d = h->d;
+  finalize_cov<<<(int)ceil_div((int64_t)d * d, 256), 256, 0, st>>>(
+      all_stats, nranks, rank, d, (long long)h->n_eff, (long long)(h->n + h->rows_total), (long long)h->start_clip,
+      h->n_stdev, h->d_mean, h->d_C, h->d_mean1, h->d_C1, h->d_lo1, h->d_hi1, ws.rank_pre, h->d_gate);
+  SB_LAUNCH_CHECK();
+  return SB_OK;
+}
+
+}  // namespace sb

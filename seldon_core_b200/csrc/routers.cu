@@ -1,0 +1,453 @@
+// Epsilon-greedy and Thompson-sampling routers, batched: T interleaved route/send_feedback calls per launch.
+//
+// Replaces components/routers/epsilon-greedy/EpsilonGreedy.py:35-136 and
+// components/routers/thompson-sampling/ThompsonSampling.py:35-115 of the reference.  Decisions must be
+// bit-identical to the reference under a seed, so both MT19937 streams it draws from are reproduced word for word
+// on the device:
+//   - CPython `random` : init_by_array seeding, 53-bit doubles from two words, _randbelow by rejection
+//                        (route: random.random(), random.choice(others); initial best_branch)
+//   - NumPy legacy     : init_genrand seeding, masked-rejection bounded integers (tie break, np.random.choice),
+//                        legacy beta = Johnk (a,b <= 1) or two Marsaglia-Tsang gammas fed by the cached polar
+//                        Gaussian (np.random.beta)
+// The bandit is sequential in time (route_t depends on feedback_{t-1}); this is a latency kernel, one warp, all
+// lanes executing the same instruction stream (the generator state lives in shared memory and is advanced
+// uniformly), lanes = arms for the tie-break scan.  It has no roofline; bench.py reports calls/s.
+#include <string.h>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int MT_N = 624, MT_M = 397;
+constexpr int kMaxArms = 1024;
+
+struct MtState {
+  uint32_t mt[MT_N];
+  int pos;
+  int has_gauss;
+  double gauss;
+};
+
+struct RouterState {
+  MtState py, np;
+  long long succ[kMaxArms];
+  long long tries[kMaxArms];
+  int best;
+};
+
+__host__ __device__ inline void mt_init_genrand(MtState* g, uint32_t s) {
+  g->mt[0] = s;
+  for (int i = 1; i < MT_N; ++i) g->mt[i] = 1812433253u * (g->mt[i - 1] ^ (g->mt[i - 1] >> 30)) + (uint32_t)i;
+  g->pos = MT_N;
+  g->has_gauss = 0;
+  g->gauss = 0.0;
+}
+
+inline void mt_init_by_array(MtState* g, const uint32_t* key, int len) {
+  mt_init_genrand(g, 19650218u);
+  uint32_t* mt = g->mt;
+  int i = 1, j = 0;
+  for (int k = MT_N > len ? MT_N : len; k; --k) {
+    mt[i] = (mt[i] ^ ((mt[i - 1] ^ (mt[i - 1] >> 30)) * 1664525u)) + key[j] + (uint32_t)j;
+    ++i; ++j;
+    if (i >= MT_N) { mt[0] = mt[MT_N - 1]; i = 1; }
+    if (j >= len) j = 0;
+  }
+  for (int k = MT_N - 1; k; --k) {
+    mt[i] = (mt[i] ^ ((mt[i - 1] ^ (mt[i - 1] >> 30)) * 1566083941u)) - (uint32_t)i;
+    ++i;
+    if (i >= MT_N) { mt[0] = mt[MT_N - 1]; i = 1; }
+  }
+  mt[0] = 0x80000000u;
+  g->pos = MT_N;
+}
+
+// ---- device-side generator working on a shared-memory copy; every lane of the warp calls these together
+struct DevMt {
+  uint32_t* mt;  // shared
+  int pos;
+  int has_gauss;
+  double gauss;
+};
+
+__device__ __forceinline__ uint32_t mt_twist_word(uint32_t cur, uint32_t nxt, uint32_t far) {
+  uint32_t y = (cur & 0x80000000u) | (nxt & 0x7fffffffu);
+  return far ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+}
+
+// regenerate the 624 words; three dependency-free phases (new[k] needs old[k], old[k+1] and old/new[k+397 mod 624])
+__device__ void mt_regenerate(uint32_t* mt) {
+  const int lane = threadIdx.x & 31;
+  __syncwarp();
+  const uint32_t first = mt[0];
+  // phase 1: k in [0, 227): uses old[k+397]
+  for (int k0 = 0; k0 < MT_N - MT_M; k0 += 32) {
+    const int k = k0 + lane;
+    uint32_t v = 0;
+    if (k < MT_N - MT_M) v = mt_twist_word(mt[k], mt[k + 1], mt[k + MT_M]);
+    __syncwarp();
+    if (k < MT_N - MT_M) mt[k] = v;
+    __syncwarp();
+  }
+  // phase 2 and 3: k in [227, 623): uses new[k-227]; chunks of <= 227 are independent of themselves
+  for (int k0 = MT_N - MT_M; k0 < MT_N - 1; k0 += 32) {
+    const int k = k0 + lane;
+    uint32_t v = 0;
+    if (k < MT_N - 1) v = mt_twist_word(mt[k], mt[k + 1], mt[k - (MT_N - MT_M)]);
+    __syncwarp();
+    if (k < MT_N - 1) mt[k] = v;
+    __syncwarp();
+  }
+  if (lane == 0) {
+    (void)first;
+    mt[MT_N - 1] = mt_twist_word(mt[MT_N - 1], mt[0], mt[MT_M - 1]);
+  }
+  __syncwarp();
+}
+
+__device__ __forceinline__ uint32_t mt_u32(DevMt& g) {
+  if (g.pos >= MT_N) {  // warp-uniform
+    mt_regenerate(g.mt);
+    g.pos = 0;
+  }
+  uint32_t y = g.mt[g.pos++];
+  y ^= y >> 11;
+  y ^= (y << 7) & 0x9d2c5680u;
+  y ^= (y << 15) & 0xefc60000u;
+  y ^= y >> 18;
+  return y;
+}
+
+__device__ __forceinline__ double mt_double(DevMt& g) {
+  const uint32_t a = mt_u32(g) >> 5, b = mt_u32(g) >> 6;
+  return ((double)a * 67108864.0 + (double)b) / 9007199254740992.0;
+}
+
+__device__ __forceinline__ uint32_t py_randbelow(DevMt& g, uint32_t n) {
+  const int k = 32 - __clz(n);
+  uint32_t r = mt_u32(g) >> (32 - k);
+  while (r >= n) r = mt_u32(g) >> (32 - k);
+  return r;
+}
+
+__device__ __forceinline__ uint32_t np_choice_index(DevMt& g, uint32_t m) {
+  const uint32_t rng = m - 1;
+  if (rng == 0) return 0;
+  uint32_t mask = rng;
+  mask |= mask >> 1; mask |= mask >> 2; mask |= mask >> 4; mask |= mask >> 8; mask |= mask >> 16;
+  for (;;) {
+    const uint32_t v = mt_u32(g) & mask;
+    if (v <= rng) return v;
+  }
+}
+
+__device__ double np_gauss(DevMt& g) {
+  if (g.has_gauss) {
+    const double t = g.gauss;
+    g.has_gauss = 0;
+    g.gauss = 0.0;
+    return t;
+  }
+  double x1, x2, r2;
+  do {
+    x1 = 2.0 * mt_double(g) - 1.0;
+    x2 = 2.0 * mt_double(g) - 1.0;
+    r2 = __dadd_rn(__dmul_rn(x1, x1), __dmul_rn(x2, x2));
+  } while (r2 >= 1.0 || r2 == 0.0);
+  const double f = sqrt(__dmul_rn(-2.0, log(r2)) / r2);
+  g.gauss = __dmul_rn(f, x1);
+  g.has_gauss = 1;
+  return __dmul_rn(f, x2);
+}
+
+__device__ double np_std_gamma(DevMt& g, double shape) {
+  if (shape == 1.0) return -log(1.0 - mt_double(g));
+  if (shape == 0.0) return 0.0;
+  if (shape < 1.0) {
+    for (;;) {
+      const double u = mt_double(g), v = -log(1.0 - mt_double(g));
+      if (u <= 1.0 - shape) {
+        const double x = pow(u, 1.0 / shape);
+        if (x <= v) return x;
+      } else {
+        const double y = -log((1 - u) / shape);
+        const double x = pow(__dadd_rn(1.0 - shape, __dmul_rn(shape, y)), 1.0 / shape);
+        if (x <= __dadd_rn(v, y)) return x;
+      }
+    }
+  }
+  const double b = shape - 1.0 / 3.0, c = 1.0 / sqrt(9 * b);
+  for (;;) {
+    double x, v;
+    do {
+      x = np_gauss(g);
+      v = __dadd_rn(1.0, __dmul_rn(c, x));
+    } while (v <= 0.0);
+    v = __dmul_rn(__dmul_rn(v, v), v);
+    const double u = mt_double(g);
+    const double x2 = __dmul_rn(x, x);
+    if (u < __dadd_rn(1.0, -__dmul_rn(__dmul_rn(0.0331, x2), x2))) return __dmul_rn(b, v);
+    // log(U) < 0.5*X*X + b*(1 - V + log(V)), evaluated without fused multiply-add like the C reference
+    const double rhs = __dadd_rn(__dmul_rn(__dmul_rn(0.5, x), x), __dmul_rn(b, __dadd_rn(__dadd_rn(1.0, -v), log(v))));
+    if (log(u) < rhs) return __dmul_rn(b, v);
+  }
+}
+
+__device__ double np_beta(DevMt& g, double a, double b) {
+  if (a <= 1.0 && b <= 1.0) {
+    for (;;) {
+      const double u = mt_double(g), v = mt_double(g);
+      const double x = pow(u, 1.0 / a), y = pow(v, 1.0 / b);
+      const double xpy = __dadd_rn(x, y);
+      if (xpy <= 1.0 && __dadd_rn(u, v) > 0.0) {
+        if (xpy > 0) return x / xpy;
+        double lx = log(u) / a, ly = log(v) / b;
+        const double lm = lx > ly ? lx : ly;
+        lx -= lm; ly -= lm;
+        return exp(lx - log(__dadd_rn(exp(lx), exp(ly))));
+      }
+    }
+  }
+  const double ga = np_std_gamma(g, a), gb = np_std_gamma(g, b);
+  return ga / __dadd_rn(ga, gb);
+}
+
+// T calls.  kind 0 = epsilon-greedy, 1 = Thompson.  reward_mode -1: route only.
+__global__ void __launch_bounds__(32)
+router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon, long long T,
+                  const long long* __restrict__ rows, const float* __restrict__ reward,
+                  const float* __restrict__ arm_p, int reward_mode, int* __restrict__ decisions, int forced_arm,
+                  double forced_reward, long long forced_rows) {
+  __shared__ uint32_t s_py[MT_N], s_np[MT_N];
+  __shared__ long long s_succ[kMaxArms], s_tries[kMaxArms];
+  __shared__ double s_val[kMaxArms];
+  const int lane = threadIdx.x;
+  for (int i = lane; i < MT_N; i += 32) { s_py[i] = st->py.mt[i]; s_np[i] = st->np.mt[i]; }
+  for (int j = lane; j < n; j += 32) {
+    s_succ[j] = st->succ[j];
+    s_tries[j] = st->tries[j];
+    s_val[j] = st->tries[j] ? (double)st->succ[j] / (double)st->tries[j] : 0.0;
+  }
+  DevMt py{s_py, st->py.pos, 0, 0.0};
+  DevMt np{s_np, st->np.pos, st->np.has_gauss, st->np.gauss};
+  int best = st->best;
+  __syncwarp();
+  for (long long t = 0; t < T; ++t) {
+    int arm;
+    if (forced_arm >= 0) {
+      arm = forced_arm;  // send_feedback for a call routed earlier
+    } else if (kind == 0) {
+      const double x = mt_double(py);  // EpsilonGreedy.py:90
+      if (x > epsilon) arm = best;
+      else {
+        const int r = (int)py_randbelow(py, (uint32_t)(n - 1));  // L91-94
+        arm = r < best ? r : r + 1;
+      }
+    } else {
+      double top = 0.0;
+      arm = 0;
+      for (int j = 0; j < n; ++j) {  // ThompsonSampling.py:81-82, arm order; np.argmax = first maximum
+        const double a = (double)(1 + s_succ[j]), b = (double)(1 + s_tries[j] - s_succ[j]);
+        const double v = np_beta(np, a, b);
+        if (j == 0 || v > top) { top = v; arm = j; }
+      }
+    }
+    if (lane == 0 && forced_arm < 0) decisions[t] = arm;
+    if (reward_mode < 0) continue;
+    const long long nrows = forced_arm >= 0 ? forced_rows : (rows ? rows[t] : 1);
+    double r;
+    if (forced_arm >= 0) r = forced_reward;
+    else if (reward_mode == 0) r = (double)reward[t];
+    else if (reward_mode == 1) r = (double)reward[t * n + arm];
+    else r = reward[t] < arm_p[arm] ? 1.0 : 0.0;
+    const long long ns = (long long)__dmul_rn(r, (double)nrows);  // int(reward * n_predictions), truncation
+    __syncwarp();
+    if (lane == 0) {
+      s_succ[arm] += ns;
+      s_tries[arm] += nrows;
+      if (kind == 0) s_val[arm] = (double)s_succ[arm] / (double)s_tries[arm];  // L118-119
+    }
+    __syncwarp();
+    if (kind == 0) {
+      // best = np.random.choice(where(values == max(values)))   L124-125
+      double top = -INFINITY;
+      for (int j = lane; j < n; j += 32) top = fmax(top, s_val[j]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) top = fmax(top, __shfl_xor_sync(0xffffffffu, top, o));
+      int m = 0;
+      for (int j0 = 0; j0 < n; j0 += 32) {
+        const int j = j0 + lane;
+        m += __popc(__ballot_sync(0xffffffffu, j < n && s_val[j] == top));
+      }
+      int pick = (int)np_choice_index(np, (uint32_t)m);
+      for (int j0 = 0; j0 < n; j0 += 32) {
+        const int j = j0 + lane;
+        const unsigned bal = __ballot_sync(0xffffffffu, j < n && s_val[j] == top);
+        const int cnt = __popc(bal);
+        if (pick < cnt) {
+          unsigned b2 = bal;
+          for (int s = 0; s < pick; ++s) b2 &= b2 - 1;
+          best = j0 + __ffs(b2) - 1;
+          break;
+        }
+        pick -= cnt;
+      }
+    }
+  }
+  __syncwarp();
+  for (int i = lane; i < MT_N; i += 32) { st->py.mt[i] = s_py[i]; st->np.mt[i] = s_np[i]; }
+  for (int j = lane; j < n; j += 32) { st->succ[j] = s_succ[j]; st->tries[j] = s_tries[j]; }
+  if (lane == 0) {
+    st->py.pos = py.pos;
+    st->np.pos = np.pos;
+    st->np.has_gauss = np.has_gauss;
+    st->np.gauss = np.gauss;
+    st->best = best;
+  }
+}
+
+}  // namespace
+
+struct sb_router {
+  int kind, n;
+  double epsilon;
+  RouterState* d_state;
+};
+
+extern "C" int32_t sb_router_create(sb_router_t** out, int32_t kind, int32_t n_branches, double epsilon, int64_t seed,
+                                    int32_t best_branch) {
+  SB_REQUIRE(out, SB_ERR_INVALID, "sb_router_create: null handle pointer");
+  SB_REQUIRE(kind == SB_ROUTER_EPSILON_GREEDY || kind == SB_ROUTER_THOMPSON, SB_ERR_INVALID, "sb_router_create: bad kind");
+  SB_REQUIRE(n_branches > 0 && n_branches <= kMaxArms, SB_ERR_INVALID, "n_branches parameter must be given (1..%d)", kMaxArms);
+  SB_REQUIRE(seed > 0 && seed <= 0xffffffffll, SB_ERR_INVALID,
+             "sb_router_create: seed must be in 1..2^32-1 (np.random.seed range; a falsy seed means unseeded in the "
+             "reference - pick one on the host)");
+  SB_REQUIRE(best_branch < n_branches, SB_ERR_INVALID, "sb_router_create: best_branch out of range");
+  RouterState* hs = new RouterState();
+  memset(hs, 0, sizeof *hs);
+  uint32_t key[2];
+  int len = 0;
+  for (uint64_t a = (uint64_t)seed; a; a >>= 32) key[len++] = (uint32_t)a;
+  mt_init_by_array(&hs->py, key, len);       // random.seed(seed)      EpsilonGreedy.py:48
+  mt_init_genrand(&hs->np, (uint32_t)seed);  // np.random.seed(seed)   EpsilonGreedy.py:49
+  hs->best = 0;
+  if (kind == SB_ROUTER_EPSILON_GREEDY) {
+    if (best_branch > 0) hs->best = best_branch;  // `if best_branch:` - 0 is falsy (EpsilonGreedy.py:64)
+    else {
+      // random.choice(range(n)): one _randbelow draw from the python stream, done on the host copy
+      MtState* g = &hs->py;
+      auto u32 = [&]() {
+        if (g->pos >= MT_N) {
+          for (int k = 0; k < MT_N; ++k) {
+            uint32_t y = (g->mt[k] & 0x80000000u) | (g->mt[(k + 1) % MT_N] & 0x7fffffffu);
+            g->mt[k] = g->mt[(k + MT_M) % MT_N] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+          }
+          g->pos = 0;
+        }
+        uint32_t y = g->mt[g->pos++];
+        y ^= y >> 11; y ^= (y << 7) & 0x9d2c5680u; y ^= (y << 15) & 0xefc60000u; y ^= y >> 18;
+        return y;
+      };
+      const uint32_t n = (uint32_t)n_branches;
+      const int k = 32 - __builtin_clz(n);
+      uint32_t r = u32() >> (32 - k);
+      while (r >= n) r = u32() >> (32 - k);
+      hs->best = (int)r;
+    }
+  }
+  sb_router* h = new sb_router{kind, n_branches, epsilon, nullptr};
+  cudaError_t e = cudaMalloc(&h->d_state, sizeof(RouterState));
+  if (e == cudaSuccess) e = cudaMemcpy(h->d_state, hs, sizeof(RouterState), cudaMemcpyHostToDevice);
+  delete hs;
+  if (e != cudaSuccess) {
+    sb::set_error("sb_router_create: %s", cudaGetErrorString(e));
+    if (h->d_state) cudaFree(h->d_state);
+    delete h;
+    return SB_ERR_CUDA;
+  }
+  *out = h;
+  return SB_OK;
+}
+
+extern "C" int32_t sb_router_destroy(sb_router_t* h) {
+  if (!h) return SB_OK;
+  cudaFree(h->d_state);
+  delete h;
+  return SB_OK;
+}
+
+extern "C" int32_t sb_router_run(sb_router_t* h, int64_t T, const int64_t* d_rows_per_call, const float* d_reward,
+                                 const float* d_arm_p, int32_t reward_mode, int32_t* d_decisions, uintptr_t stream) {
+  SB_REQUIRE(h && T >= 0 && reward_mode >= -1 && reward_mode <= 2, SB_ERR_INVALID, "sb_router_run: bad arguments");
+  if (T == 0) return SB_OK;
+  SB_REQUIRE(d_decisions, SB_ERR_INVALID, "sb_router_run: null decisions");
+  SB_REQUIRE(reward_mode < 0 || d_reward, SB_ERR_INVALID, "sb_router_run: rewards required");
+  SB_REQUIRE(reward_mode != SB_REWARD_BERNOULLI || d_arm_p, SB_ERR_INVALID, "sb_router_run: arm probabilities required");
+  SB_REQUIRE(!(h->kind == SB_ROUTER_EPSILON_GREEDY && h->n < 2), SB_ERR_INVALID,
+             "epsilon-greedy needs >= 2 branches to explore (reference raises IndexError on random.choice([]))");
+  router_run_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, (long long)T,
+                                                       (const long long*)d_rows_per_call, d_reward, d_arm_p,
+                                                       reward_mode, d_decisions, -1, 0.0, 0);
+  SB_LAUNCH_CHECK();
+  return SB_OK;
+}
+
+extern "C" int32_t sb_router_feedback(sb_router_t* h, int32_t arm, int64_t rows, double reward, uintptr_t stream) {
+  SB_REQUIRE(h && arm >= 0 && arm < h->n, SB_ERR_INVALID, "sb_router_feedback: routing %d outside 0..%d", arm,
+             h ? h->n - 1 : 0);
+  SB_REQUIRE(rows >= 1, SB_ERR_INVALID, "sb_router_feedback: rows must be >= 1 (reference divides by tries)");
+  router_run_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, 1, nullptr, nullptr,
+                                                       nullptr, 0, nullptr, arm, reward, (long long)rows);
+  SB_LAUNCH_CHECK();
+  return SB_OK;
+}
+
+extern "C" int64_t sb_router_state_len(const sb_router_t* h) {
+  return h ? 2 * (int64_t)h->n + 1 + (MT_N + 1) + (MT_N + 3) : 0;
+}
+
+extern "C" int32_t sb_router_get_state(sb_router_t* h, int64_t* out, uintptr_t stream) {
+  SB_REQUIRE(h && out, SB_ERR_INVALID, "sb_router_get_state: bad arguments");
+  RouterState* hs = new RouterState();
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemcpyAsync(hs, h->d_state, sizeof(RouterState), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) { delete hs; sb::set_error("sb_router_get_state: %s", cudaGetErrorString(e)); return SB_ERR_CUDA; }
+  int64_t* p = out;
+  for (int j = 0; j < h->n; ++j) *p++ = hs->succ[j];
+  for (int j = 0; j < h->n; ++j) *p++ = hs->tries[j];
+  *p++ = hs->best;
+  for (int i = 0; i < MT_N; ++i) *p++ = hs->py.mt[i];
+  *p++ = hs->py.pos;
+  for (int i = 0; i < MT_N; ++i) *p++ = hs->np.mt[i];
+  *p++ = hs->np.pos;
+  *p++ = hs->np.has_gauss;
+  long long bits;
+  memcpy(&bits, &hs->np.gauss, 8);
+  *p++ = bits;
+  delete hs;
+  return SB_OK;
+}
+
+extern "C" int32_t sb_router_set_state(sb_router_t* h, const int64_t* in, uintptr_t stream) {
+  SB_REQUIRE(h && in, SB_ERR_INVALID, "sb_router_set_state: bad arguments");
+  RouterState* hs = new RouterState();
+  memset(hs, 0, sizeof *hs);
+  const int64_t* p = in;
+  for (int j = 0; j < h->n; ++j) hs->succ[j] = *p++;
+  for (int j = 0; j < h->n; ++j) hs->tries[j] = *p++;
+  hs->best = (int)*p++;
+  for (int i = 0; i < MT_N; ++i) hs->py.mt[i] = (uint32_t)*p++;
+  hs->py.pos = (int)*p++;
+  for (int i = 0; i < MT_N; ++i) hs->np.mt[i] = (uint32_t)*p++;
+  hs->np.pos = (int)*p++;
+  hs->np.has_gauss = (int)*p++;
+  long long bits = *p++;
+  memcpy(&hs->np.gauss, &bits, 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemcpyAsync(h->d_state, hs, sizeof(RouterState), cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  delete hs;
+  if (e != cudaSuccess) { sb::set_error("sb_router_set_state: %s", cudaGetErrorString(e)); return SB_ERR_CUDA; }
+  return SB_OK;
+}

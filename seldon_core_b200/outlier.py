@@ -1,0 +1,333 @@
+"""Drop-in for the reference's online Mahalanobis outlier detector, computed on a B200.
+
+Mirrors ``components/outlier-detection/mahalanobis/CoreMahalanobis.py`` of the reference: same constructor
+parameters (L26), same methods (``predict`` L42, ``transform_input`` L54, ``send_feedback`` L154, ``tags`` L168,
+``metrics`` L180) and the same public attributes (``threshold, n_components, max_n, n_stdev, start_clip, clip,
+mean, C, n, nb_outliers, score, prediction``).  The arithmetic of ``_get_preds`` (L68-151) runs in libsb200.so
+through the C ABI of ``include/sb200.h``; PyTorch only owns the device buffers and the stream.
+
+Deliberate differences: scores are computed in fp32 (tolerance 1e-4 relative), the warm-up gate has
+a rank guard, ``max_n=1`` is rejected (the reference raises ZeroDivisionError at L134), and at most 32 principal
+components are supported.
+"""
+import ctypes
+import threading
+
+import numpy as np
+
+from . import _cabi
+from .errors import SeldonB200Error
+
+
+class OutlierMahalanobisB200(object):
+    def __init__(self, threshold=25, n_components=3, n_stdev=3, start_clip=50, max_n=-1, device=None):
+        self.threshold = threshold
+        self.n_components = n_components
+        self.max_n = max_n
+        self.n_stdev = n_stdev
+        self.start_clip = start_clip
+        self.nb_outliers = 0
+        self._device = device
+        self._h = None
+        self._d = None
+        self._ws = None
+        self._lock = threading.RLock()
+        self._restore = None
+        self._score_t = None
+        self._flag_t = None
+        self._options = {}
+
+    # ------------------------------------------------------------------ reference API
+    def predict(self, X, feature_names=None):
+        """Return outlier predictions (CoreMahalanobis.py:42-51): int array of 0/1, one per row."""
+        return self._get_preds(X)
+
+    def transform_input(self, X, feature_names=None):
+        """Detect outliers, keep them for tags(), return the input unchanged (L54-65)."""
+        self.prediction_meta = self._get_preds(X)
+        return X
+
+    def send_feedback(self, X, feature_names, reward, truth):
+        return []  # L154-165
+
+    def tags(self):
+        try:
+            return {"outlier-predictions": self.prediction_meta.tolist()}  # L168-177
+        except AttributeError:
+            return None
+
+    def metrics(self):
+        """Six gauges averaged over the last batch; mutates nb_outliers like the reference (L180-192)."""
+        with self._lock:
+            nrows, n_flagged, score_sum = self._last_sums()
+            self.nb_outliers += n_flagged
+            g = lambda key, value: {"type": "GAUGE", "key": key, "value": value}
+            return [
+                g("is_outlier", n_flagged / nrows),
+                g("outlier_score", score_sum / nrows),
+                g("nb_outliers", int(self.nb_outliers)),
+                g("fraction_outliers", int(self.nb_outliers) / self.n),
+                g("observation", self.n),
+                g("threshold", self.threshold),
+            ]
+
+    # ------------------------------------------------------------------ public attributes of the reference
+    @property
+    def n(self):
+        if self._h is None:
+            return self._restore["n"] if self._restore else 0
+        return self._state()["n"]
+
+    @property
+    def mean(self):
+        st = self._state()
+        return st["mean"] if st["has_state"] else 0  # L35: scalar 0 until the first batch
+
+    @property
+    def C(self):
+        st = self._state()
+        return st["C"] if st["has_state"] else 0
+
+    @property
+    def clip(self):
+        st = self._state()
+        return [st["clip_lo"], st["clip_hi"]] if st["has_clip"] else None
+
+    @property
+    def score(self):
+        if self._score_t is None:
+            raise AttributeError("score")
+        return self._score_t.double().cpu().numpy()
+
+    @property
+    def prediction(self):
+        if self._flag_t is None:
+            raise AttributeError("prediction")
+        return self._flag_t.cpu().numpy().astype(int)
+
+    # ------------------------------------------------------------------ device path
+    def set_option(self, option, value):
+        """SB_OPT_* knob of include/sb200.h (applied when the handle exists)."""
+        self._options[option] = value
+        if self._h is not None:
+            _cabi.check(_cabi.lib().sb_maha_set_option(self._h, option, value))
+
+    def score_device(self, X):
+        """One request batch resident on the GPU: X is a CUDA float32 tensor (rows, d), row-major.
+
+        Returns (score float32[rows], flag int32[rows]) CUDA tensors; no host synchronisation."""
+        import torch
+
+        with self._lock:
+            if not (isinstance(X, torch.Tensor) and X.is_cuda and X.dtype == torch.float32 and X.dim() == 2):
+                raise SeldonB200Error("score_device expects a 2-D CUDA float32 tensor")
+            if X.stride(1) != 1:
+                X = X.contiguous()
+            rows, d = X.shape
+            if rows < 1:
+                raise SeldonB200Error("empty batch")
+            self._ensure_handle(d, X.device)
+            L = _cabi.lib()
+            ws = self._workspace(rows)
+            score = torch.empty(rows, dtype=torch.float32, device=X.device)
+            flag = torch.empty(rows, dtype=torch.int32, device=X.device)
+            with torch.cuda.device(X.device):
+                st = torch.cuda.current_stream().cuda_stream
+                rc = L.sb_maha_batch(self._h, X.data_ptr(), rows, X.stride(0), score.data_ptr(), flag.data_ptr(),
+                                     ws.data_ptr(), ws.numel(), st)
+            if rc != 0:
+                L.sb_maha_abort_batch(self._h)
+            _cabi.check(rc)
+            self._score_t, self._flag_t = score, flag
+            self._cached_state = None
+            return score, flag
+
+    # two-phase form for row-sharded batches (seldon_core_b200/dist.py)
+    def pass1_device(self, X, stats_out):
+        import torch
+
+        rows, d = X.shape
+        self._ensure_handle(d, X.device)
+        ws = self._workspace(rows)
+        with torch.cuda.device(X.device):
+            _cabi.check(_cabi.lib().sb_maha_pass1_stats(self._h, X.data_ptr(), rows, X.stride(0), ws.data_ptr(),
+                                                        ws.numel(), stats_out.data_ptr(),
+                                                        torch.cuda.current_stream().cuda_stream))
+
+    def finish_device(self, X, all_stats, nranks, rank, total_rows, row0):
+        import torch
+
+        rows = X.shape[0]
+        L = _cabi.lib()
+        ws = self._workspace(rows)
+        score = torch.empty(rows, dtype=torch.float32, device=X.device)
+        flag = torch.empty(rows, dtype=torch.int32, device=X.device)
+        with torch.cuda.device(X.device):
+            st = torch.cuda.current_stream().cuda_stream
+            try:
+                _cabi.check(L.sb_maha_finalize(self._h, all_stats.data_ptr(), nranks, rank, total_rows, row0,
+                                               ws.data_ptr(), ws.numel(), st))
+                _cabi.check(L.sb_maha_pass2_score(self._h, X.data_ptr(), rows, X.stride(0), score.data_ptr(),
+                                                  flag.data_ptr(), ws.data_ptr(), ws.numel(), st))
+                _cabi.check(L.sb_maha_commit(self._h, st))
+            except Exception:
+                L.sb_maha_abort_batch(self._h)
+                raise
+        self._score_t, self._flag_t = score, flag
+        self._cached_state = None
+        return score, flag
+
+    def stats_len(self, d):
+        return 1 + d + d * d
+
+    # ------------------------------------------------------------------ internals
+    def _get_preds(self, X):
+        import torch
+
+        with self._lock:
+            dev = self._pick_device()
+            if isinstance(X, torch.Tensor):
+                Xd = X.to(device=dev, dtype=torch.float32)
+            else:
+                Xn = np.asarray(X)
+                if Xn.ndim != 2:
+                    raise SeldonB200Error("expected a 2-D batch, got shape %s" % (Xn.shape,))
+                if Xn.dtype == np.float64:
+                    # the request payload is float64 (utils.py:161-176): ship the 8-byte values and narrow on the device
+                    raw = torch.from_numpy(np.ascontiguousarray(Xn)).to(dev, non_blocking=True)
+                    Xd = torch.empty(Xn.shape, dtype=torch.float32, device=dev)
+                    with torch.cuda.device(dev):
+                        _cabi.check(_cabi.lib().sb_unpack_tensor_f64(raw.data_ptr(), 0, Xn.shape[0], Xn.shape[1], None,
+                                                                     None, Xd.data_ptr(), Xn.shape[1],
+                                                                     torch.cuda.current_stream().cuda_stream))
+                else:
+                    Xd = torch.from_numpy(np.ascontiguousarray(Xn, dtype=np.float32)).to(dev, non_blocking=True)
+            _, flag = self.score_device(Xd)
+            return flag.cpu().numpy().astype(int)
+
+    def _pick_device(self):
+        import torch
+
+        if not torch.cuda.is_available():
+            raise SeldonB200Error("no CUDA device: seldon_core_b200 has no CPU fallback", status_code=500)
+        if self._device is None:
+            self._device = torch.device("cuda", torch.cuda.current_device())
+        return torch.device(self._device)
+
+    def _ensure_handle(self, d, device):
+        if self._h is not None:
+            if d != self._d:
+                raise SeldonB200Error("feature count changed from %d to %d" % (self._d, d))
+            return
+        import torch
+
+        self._device = device
+        L = _cabi.lib()
+        h = ctypes.c_void_p()
+        with torch.cuda.device(device):
+            _cabi.check(L.sb_maha_create(ctypes.byref(h), d, int(self.n_components), float(self.threshold),
+                                         float(self.n_stdev), int(self.start_clip), int(self.max_n)))
+        self._h, self._d = h, d
+        for opt, val in self._options.items():
+            _cabi.check(L.sb_maha_set_option(self._h, opt, val))
+        self._cached_state = None
+        if self._restore is not None:
+            self._push_state(self._restore)
+            self._restore = None
+
+    def _workspace(self, rows):
+        import torch
+
+        need = ctypes.c_uint64()
+        _cabi.check(_cabi.lib().sb_maha_workspace_bytes(self._h, rows, ctypes.byref(need)))
+        if self._ws is None or self._ws.numel() < need.value:
+            self._ws = torch.empty(int(need.value), dtype=torch.uint8, device=self._device)
+        return self._ws
+
+    def _state(self):
+        if self._h is None:
+            if self._restore is not None:
+                return self._restore
+            return {"n": 0, "has_state": 0, "has_clip": 0, "mean": None, "C": None, "clip_lo": None, "clip_hi": None}
+        if getattr(self, "_cached_state", None) is not None:
+            return self._cached_state
+        import torch
+
+        d = self._d
+        mean, C, lo, hi = np.empty(d), np.empty((d, d)), np.empty(d), np.empty(d)
+        n, hs, hc = ctypes.c_int64(), ctypes.c_int32(), ctypes.c_int32()
+        with torch.cuda.device(self._device):
+            _cabi.check(_cabi.lib().sb_maha_get_state(self._h, mean.ctypes.data, C.ctypes.data, lo.ctypes.data,
+                                                      hi.ctypes.data, ctypes.byref(n), ctypes.byref(hs),
+                                                      ctypes.byref(hc), torch.cuda.current_stream().cuda_stream))
+        self._cached_state = {"n": n.value, "has_state": hs.value, "has_clip": hc.value, "mean": mean, "C": C,
+                              "clip_lo": lo, "clip_hi": hi}
+        return self._cached_state
+
+    def _push_state(self, st):
+        import torch
+
+        p = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float64).ctypes.data
+        keep = [np.ascontiguousarray(st[k], dtype=np.float64) if st[k] is not None else None
+                for k in ("mean", "C", "clip_lo", "clip_hi")]
+        with torch.cuda.device(self._device):
+            _cabi.check(_cabi.lib().sb_maha_set_state(
+                self._h, *[None if a is None else a.ctypes.data for a in keep], int(st["n"]), int(st["has_state"]),
+                int(st["has_clip"]), torch.cuda.current_stream().cuda_stream))
+        self._cached_state = None
+
+    def _last_sums(self):
+        import torch
+
+        if self._h is None or self._flag_t is None:
+            raise AttributeError("prediction")
+        nf, ss, gr = ctypes.c_int64(), ctypes.c_double(), ctypes.c_int64()
+        with torch.cuda.device(self._device):
+            _cabi.check(_cabi.lib().sb_maha_last_batch_sums(self._h, ctypes.byref(nf), ctypes.byref(ss), ctypes.byref(gr),
+                                                            torch.cuda.current_stream().cuda_stream))
+        self.gate_row = gr.value
+        return self._flag_t.numel(), nf.value, ss.value
+
+    def eigvecs(self):
+        """Top-k eigenvectors used by the last batch, (d, k) - diagnostics and subspace parity tests."""
+        import torch
+
+        k = min(int(self.n_components), self._d)
+        V = np.empty((self._d, k))
+        with torch.cuda.device(self._device):
+            _cabi.check(_cabi.lib().sb_maha_get_eigvecs(self._h, V.ctypes.data, torch.cuda.current_stream().cuda_stream))
+        return V
+
+    # ------------------------------------------------------------------ persistence (python/seldon_core/persistence.py:84)
+    def __getstate__(self):
+        with self._lock:
+            st = dict(self._state())
+            out = {k: v for k, v in self.__dict__.items() if not k.startswith("_")}
+            out["_saved"] = st
+            out["_saved_d"] = self._d
+            out["_saved_options"] = dict(self._options)
+            return out
+
+    def __setstate__(self, state):
+        saved = state.pop("_saved")
+        d = state.pop("_saved_d")
+        opts = state.pop("_saved_options", {})
+        self.__dict__.update(state)
+        self._device = None
+        self._h = None
+        self._d = None
+        self._ws = None
+        self._lock = threading.RLock()
+        self._score_t = None
+        self._flag_t = None
+        self._options = opts
+        self._restore = saved if d is not None else None
+        self._restore_d = d
+
+    def __del__(self):
+        try:
+            if self._h is not None:
+                _cabi.lib().sb_maha_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass

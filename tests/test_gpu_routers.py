@@ -1,0 +1,87 @@
+"""GPU parity of the routers: decisions bit-exact against the fixtures produced by the unmodified reference classes."""
+import glob
+import os
+import pickle
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from oracle import routers as R
+from seldon_core_b200 import EpsilonGreedyB200, ThompsonSamplingB200, _cabi, synth
+
+from conftest import GOLDEN
+
+CASES = sorted(os.path.basename(p)[7:-4] for p in glob.glob(os.path.join(GOLDEN, "router_*.npz")))
+
+
+def make(g):
+    kind, n, seed = int(g["kind"]), int(g["n_branches"]), int(g["seed"])
+    if kind == 0:
+        return EpsilonGreedyB200(n_branches=n, epsilon=float(g["epsilon"]), seed=seed)
+    return ThompsonSamplingB200(n_branches=n, seed=seed)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_batched_decisions_match_reference(name):
+    g = np.load(os.path.join(GOLDEN, "router_%s.npz" % name))
+    r = make(g)
+    n, T = int(g["n_branches"]), int(g["T"])
+    if int(g["kind"]) == 0:
+        assert r.best_branch == int(g["init_best"])
+    dec = r.run_batched(T, g["u"], reward_mode=_cabi.SB_REWARD_BERNOULLI, arm_p=g["arm_p"], rows_per_call=g["rows"])
+    assert np.array_equal(dec.cpu().numpy(), g["decisions"])
+    assert r.branch_success == g["success"].tolist() and r.branch_tries == g["tries"].tolist()
+    if int(g["kind"]) == 0:
+        assert r.best_branch == int(g["final_best"])
+
+
+@pytest.mark.parametrize("name", ["eps_3_rows", "thompson_2_rows"])
+def test_call_by_call_api_and_both_feedback_orders(name):
+    g = np.load(os.path.join(GOLDEN, "router_%s.npz" % name))
+    r = make(g)
+
+    class Feat:
+        def __init__(self, rows):
+            self.shape = (rows, 4)
+
+    for t in range(300):
+        a = r.route(None, None)
+        assert type(a) is int and a == int(g["decisions"][t])          # seldon_methods.py:231 wants a Python int
+        rew = 1.0 if g["u"][t] < g["arm_p"][a] else 0.0
+        if t % 2:
+            r.send_feedback(Feat(int(g["rows"][t])), None, a, rew, None)              # component order
+        else:
+            r.send_feedback(Feat(int(g["rows"][t])), None, rew, None, routing=a)      # wrapper order
+    # persistence: a restored router continues the identical sequence
+    r2 = pickle.loads(pickle.dumps(r))
+    for t in range(300, 400):
+        a, b = r.route(None, None), r2.route(None, None)
+        assert a == b == int(g["decisions"][t])
+        rew = 1.0 if g["u"][t] < g["arm_p"][a] else 0.0
+        r.send_feedback(Feat(int(g["rows"][t])), None, a, rew, None)
+        r2.send_feedback(Feat(int(g["rows"][t])), None, a, rew, None)
+
+
+def test_c4_shape_against_c_oracle():
+    """BASELINE config 4 shape (32 arms, seed 1, interleaved route/feedback) on 1 M eps-greedy and 100 k Thompson calls."""
+    for kind, T in ((0, 1000000), (1, 100000)):
+        p, u = synth.router_rewards(T, 32)
+        ref, st = R.run_batched(kind, 32, 0.1, 1, 0, T, reward=u, reward_mode=R.REWARD_BERNOULLI, arm_p=p)
+        r = EpsilonGreedyB200(n_branches=32, epsilon=0.1, seed=1) if kind == 0 else ThompsonSamplingB200(n_branches=32, seed=1)
+        dec = r.run_batched(T, u, reward_mode=_cabi.SB_REWARD_BERNOULLI, arm_p=p).cpu().numpy()
+        assert np.array_equal(dec, ref), "first mismatch at call %d" % int(np.flatnonzero(dec != ref)[0])
+        assert r.branch_success == st[:32].tolist() and r.branch_tries == st[32:64].tolist()
+
+
+def test_statistics_like_reference_test():
+    """test_EpsilonGreedy.py:21-25: without feedback the best branch is chosen ~ (1 - eps) of the time."""
+    r = EpsilonGreedyB200(n_branches=3, epsilon=0.1, seed=1)
+    first = r.best_branch
+    import torch
+
+    dec = torch.empty(100000, dtype=torch.int32, device="cuda")
+    _cabi.check(_cabi.lib().sb_router_run(r._handle(), 100000, None, None, None, -1, dec.data_ptr(), r._stream()))
+    frac = float((dec == first).float().mean().item())
+    assert np.isclose(frac, 0.9, atol=0, rtol=0.01)

@@ -1,0 +1,132 @@
+"""Host-side logic that needs no GPU: drop-in constructors, argument conventions, sharding algebra (gloo, 2 ranks)."""
+import os
+import pickle
+import socket
+
+import numpy as np
+import pytest
+
+import seldon_core_b200 as s
+from seldon_core_b200 import dist as sdist
+from seldon_core_b200.errors import SeldonB200Error
+
+
+def test_constructor_signatures_match_reference():
+    import inspect
+
+    sig = inspect.signature(s.OutlierMahalanobisB200.__init__)
+    assert list(sig.parameters)[1:6] == ["threshold", "n_components", "n_stdev", "start_clip", "max_n"]
+    d = {k: v.default for k, v in sig.parameters.items()}
+    assert (d["threshold"], d["n_components"], d["n_stdev"], d["start_clip"], d["max_n"]) == (25, 3, 3, 50, -1)
+    sig = inspect.signature(s.EpsilonGreedyB200.__init__)
+    assert list(sig.parameters)[1:8] == ["n_branches", "epsilon", "best_branch", "verbose", "seed", "history",
+                                         "branch_names"]
+    sig = inspect.signature(s.ThompsonSamplingB200.__init__)
+    assert list(sig.parameters)[1:6] == ["n_branches", "verbose", "seed", "history", "branch_names"]
+    for cls, meths in ((s.OutlierMahalanobisB200, ("predict", "transform_input", "send_feedback", "tags", "metrics")),
+                       (s.EpsilonGreedyB200, ("route", "send_feedback", "n_success_failures")),
+                       (s.MeanCombinerB200, ("aggregate",)), (s.StandardiseB200, ("transform_input",))):
+        for m in meths:
+            assert callable(getattr(cls, m))
+
+
+def test_router_constructor_errors_mirror_reference():
+    # components/routers/epsilon-greedy/test_EpsilonGreedy.py:6-12
+    with pytest.raises(TypeError):
+        s.EpsilonGreedyB200()
+    with pytest.raises(AssertionError):
+        s.EpsilonGreedyB200(n_branches=-1)
+    eg = s.EpsilonGreedyB200(n_branches=3, epsilon=0.15, seed=1, branch_names="a:b:c")
+    assert eg.n_branches == 3 and eg.epsilon == 0.15 and eg.branch_names == ["a", "b", "c"]
+
+
+def test_fresh_detector_attributes_and_tags():
+    det = s.OutlierMahalanobisB200()
+    assert det.n == 0 and det.mean == 0 and det.C == 0 and det.clip is None and det.nb_outliers == 0
+    assert det.tags() is None
+    assert det.send_feedback(None, None, 1.0, None) == []
+    det2 = pickle.loads(pickle.dumps(det))
+    assert det2.n == 0 and det2.threshold == 25
+
+
+def test_combiner_shape_errors_without_gpu():
+    c = s.MeanCombinerB200()
+    with pytest.raises(SeldonB200Error, match="no inputs"):
+        c.aggregate([], [])
+    with pytest.raises(SeldonB200Error, match="not 2 dimensional"):
+        c.aggregate([np.zeros(3)], [])
+    with pytest.raises(SeldonB200Error, match="Expected batch length"):
+        c.aggregate([np.zeros((1, 2)), np.zeros((1, 3))], [])
+
+
+def test_error_type_is_wrapper_compatible():
+    e = SeldonB200Error("boom")
+    assert e.status_code == 400 and e.to_dict()["status"]["info"] == "boom"
+    assert e.to_dict()["status"]["reason"] == "MICROSERVICE_BAD_DATA"
+
+
+def test_shard_bounds_cover_the_batch():
+    for total, world in ((10, 3), (16, 8), (7, 8), (1 << 24, 8)):
+        edges = [sdist.shard_bounds(total, world, r) for r in range(world)]
+        assert edges[0][0] == 0 and edges[-1][1] == total
+        assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
+
+
+def _free_port():
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        return sk.getsockname()[1]
+
+
+def _gloo_worker(rank, world, port, total_rows, d, out):
+    import torch
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle.mahalanobis import MahalanobisLean
+
+        X = np.random.RandomState(0).randn(total_rows, d)
+        m0 = np.zeros(d)
+        r0, r1 = sdist.shard_bounds(total_rows, world, rank)
+        lean = MahalanobisLean(n_components=2)
+        sv, G = lean._stats(np.ascontiguousarray(X[r0:r1]), m0)
+        local = torch.tensor(np.concatenate([[r1 - r0], sv, G.ravel()]), dtype=torch.float64)
+        allst = sdist.gather_stats(local)
+        total, prefix = sdist.combine_stats_reference(allst.numpy(), rank)
+        out.put((rank, total, prefix))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_two_rank_stats_exchange_matches_single_call():
+    """World size 2 on CPU: the gathered per-shard (count, sum, Gram) records add up to the single-call statistics
+    and rank 1's prefix is rank 0's record (the only collective on the path)."""
+    import torch.multiprocessing as mp
+
+    from oracle.mahalanobis import MahalanobisLean
+
+    total_rows, d, world = 101, 5, 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, world, port, total_rows, d, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = {}
+    for _ in range(world):
+        rank, total, prefix = q.get(timeout=120)
+        res[rank] = (total, prefix)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    X = np.random.RandomState(0).randn(total_rows, d)
+    sv, G = MahalanobisLean(n_components=2)._stats(X, np.zeros(d))
+    whole = np.concatenate([[total_rows], sv, G.ravel()])
+    assert np.allclose(res[0][0], whole, rtol=1e-12, atol=1e-12) and np.allclose(res[1][0], whole, rtol=1e-12)
+    assert np.all(res[0][1] == 0)
+    r0, r1 = sdist.shard_bounds(total_rows, world, 0)
+    s0, G0 = MahalanobisLean(n_components=2)._stats(np.ascontiguousarray(X[r0:r1]), np.zeros(d))
+    assert np.allclose(res[1][1], np.concatenate([[r1 - r0], s0, G0.ravel()]), rtol=1e-12, atol=1e-12)
