@@ -198,8 +198,6 @@ def test_full_size_properties_c2():
     m0, n0 = det.mean.copy(), det.n
     s1, f1 = det.score_device(X)
     assert det.n == n0 + nb
-    xc = torch.clamp(X, torch.tensor(det_clip_lo(det, 0), device=dev), torch.tensor(det_clip_hi(det, 0), device=dev)) \
-        if False else None  # clipping bounds changed with the commit; (b) is checked on the unclipped bound below
     batch_mean = X.double().mean(dim=0).cpu().numpy()
     expect = m0 + nb / (n0 + nb) * (batch_mean - m0)
     assert np.max(np.abs(det.mean - expect)) < 5e-3      # clipping moves the mean by less than this
@@ -208,11 +206,3 @@ def test_full_size_properties_c2():
     _, nf, ss = det._last_sums()
     assert nf == nflag and abs(ss - ssum) <= 1e-9 * abs(ssum)
     assert torch.isfinite(s1).all() and float(s1.min()) >= 0.0
-
-
-def det_clip_lo(det, _):
-    return det.clip[0].astype(np.float32)
-
-
-def det_clip_hi(det, _):
-    return det.clip[1].astype(np.float32)
