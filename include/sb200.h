@@ -121,6 +121,9 @@ int32_t sb_maha_set_state(sb_maha_t* h, const double* h_mean, const double* h_C,
  * warm-up gate opened (-1: never) - diagnostics. */
 int32_t sb_maha_last_batch_sums(sb_maha_t* h, int64_t* n_flagged, double* score_sum, int64_t* gate_row,
                                 uintptr_t stream);
+/* diagnostics: out8 = { first open sub-segment, gate row, flagged rows, Jacobi sweeps, batch rows,
+ * sub-segments, sub-segment length, 0 } of the last batch.  Synchronises. */
+int32_t sb_maha_debug_counters(sb_maha_t* h, int64_t* out8, uintptr_t stream);
 /* top-k eigenvectors of the last batch, d x k row-major (diagnostics / subspace parity tests) */
 int32_t sb_maha_get_eigvecs(sb_maha_t* h, double* h_V, uintptr_t stream);
 /* tuning knobs: SB_OPT_GRAM_TERMS 1|3 (TF32 products per Gram element, default 3),

@@ -17,8 +17,10 @@
 /* Rank guard (deliberate, documented deviation - DESIGN.md "warm-up gate"): a matrix whose smallest LU
  * pivot is below SBO_RANK_TOL x the largest is treated as singular whatever its determinant says.  On a
  * rank-deficient proj_cov the reference's own |det| is rounding noise (9.7e-9 against the 1e-8 threshold at
- * d=64,k=16,row 16 of a cold start), so without the guard the opening row would be decided by noise. */
-#define SBO_RANK_TOL 1e-9
+ * d=64,k=16,row 16 of a cold start), so without the guard the opening row would be decided by noise.  The
+ * tolerance sits just above fp64 rounding (pivots of a singular matrix come out near 1e-16 x the largest), so a
+ * genuinely full-rank but badly scaled matrix still opens the gate exactly as in the reference. */
+#define SBO_RANK_TOL 1e-12
 
 static inline double clipd(double x, double lo, double hi) { return x < lo ? lo : (x > hi ? hi : x); }
 

@@ -26,7 +26,7 @@ import numpy as np
 import scipy.linalg
 
 _EPSILON = 1e-8  # CoreMahalanobis.py:120
-_RANK_TOL = 1e-9  # rank guard of the warm-up gate, see maha_lean.c / DESIGN.md
+_RANK_TOL = 1e-12  # rank guard of the warm-up gate, see maha_lean.c / DESIGN.md
 
 
 def gate_open(P):

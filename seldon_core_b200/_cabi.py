@@ -43,6 +43,7 @@ SIGNATURES = {
     "sb_maha_get_state": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int32), POINTER(c_int32), _uintptr]),
     "sb_maha_set_state": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, _uintptr]),
     "sb_maha_last_batch_sums": (c_int32, [c_void_p, POINTER(c_int64), POINTER(c_double), POINTER(c_int64), _uintptr]),
+    "sb_maha_debug_counters": (c_int32, [c_void_p, c_void_p, _uintptr]),
     "sb_maha_get_eigvecs": (c_int32, [c_void_p, c_void_p, _uintptr]),
     "sb_maha_set_option": (c_int32, [c_void_p, c_int32, c_int64]),
     "sb_router_create": (c_int32, [_pp, c_int32, c_int32, c_double, c_int64, c_int32]),

@@ -61,7 +61,7 @@ jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, doub
         }
         al = warp_sum(al); be = warp_sum(be); ga = warp_sum(ga);
         if (al == 0.0 || be == 0.0) continue;
-        if (fabs(ga) <= 1e-15 * sqrt(al * be)) continue;
+        if (fabs(ga) <= 1e-13 * sqrt(al * be)) continue;  // columns orthogonal to working accuracy
         const double zeta = (be - al) / (2.0 * ga);
         const double tt = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
         const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;

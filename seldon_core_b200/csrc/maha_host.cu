@@ -290,6 +290,18 @@ extern "C" int32_t sb_maha_last_batch_sums(sb_maha_t* h, int64_t* n_flagged, dou
   return SB_OK;
 }
 
+extern "C" int32_t sb_maha_debug_counters(sb_maha_t* h, int64_t* out8, uintptr_t stream) {
+  SB_REQUIRE(h && out8, SB_ERR_INVALID, "sb_maha_debug_counters: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  long long g[8];
+  SB_CUDA(cudaMemcpyAsync(g, h->d_gate, sizeof g, cudaMemcpyDeviceToHost, st));
+  SB_CUDA(cudaStreamSynchronize(st));
+  for (int i = 0; i < 8; ++i) out8[i] = g[i];
+  out8[5] = h->lay.nsub;
+  out8[6] = h->lay.sublen;
+  return SB_OK;
+}
+
 extern "C" int32_t sb_maha_get_eigvecs(sb_maha_t* h, double* h_V, uintptr_t stream) {
   SB_REQUIRE(h && h_V, SB_ERR_INVALID, "sb_maha_get_eigvecs: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;

@@ -71,7 +71,47 @@ def timings():
                 bool(torch.equal(f.to(torch.int8), labels))))
 
 
+def stages():
+    """CUDA-event time of each C-ABI stage of one 16 Mi x 64 batch."""
+    import ctypes
+
+    dev = torch.device("cuda")
+    L = _cabi.lib()
+    for nb in (1 << 20, 1 << 24):
+        prime, _ = synth.maha_rows_torch(1 << 20, 64, 16, 101, dev)
+        X, _ = synth.maha_rows_torch(nb, 64, 16, 102, dev)
+        det = OutlierMahalanobisB200(n_components=16)
+        det.score_device(prime)
+        h = det._h
+        ws = det._workspace(nb)
+        score = torch.empty(nb, dtype=torch.float32, device=dev)
+        flag = torch.empty(nb, dtype=torch.int32, device=dev)
+        st = torch.cuda.current_stream().cuda_stream
+        for it in range(3):
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+            ev[0].record()
+            _cabi.check(L.sb_maha_pass1_stats(h, X.data_ptr(), nb, 64, ws.data_ptr(), ws.numel(), None, st))
+            ev[1].record()
+            _cabi.check(L.sb_maha_finalize(h, None, 1, 0, nb, 0, ws.data_ptr(), ws.numel(), st))
+            ev[2].record()
+            _cabi.check(L.sb_maha_pass2_score(h, X.data_ptr(), nb, 64, score.data_ptr(), flag.data_ptr(), ws.data_ptr(),
+                                              ws.numel(), st))
+            ev[3].record()
+            _cabi.check(L.sb_maha_commit(h, st))
+            ev[4].record()
+            torch.cuda.synchronize()
+            c = (ctypes.c_int64 * 8)()
+            _cabi.check(L.sb_maha_debug_counters(h, c, st))
+            print("nb=%d it=%d pass1+reduce %.3f ms | finalize(cov+eigh+prefix) %.3f ms | pass2 %.3f ms | commit %.3f ms"
+                  " | sweeps=%d nsub=%d sublen=%d bstar=%d" % (
+                      nb, it, ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[2].elapsed_time(ev[3]),
+                      ev[3].elapsed_time(ev[4]), c[3], c[5], c[6], c[0]))
+
+
 if __name__ == "__main__":
     print(torch.cuda.get_device_name(0))
+    if "--stages" in sys.argv:
+        stages()
+        sys.exit(0)
     fixtures()
     timings()
