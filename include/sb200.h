@@ -121,15 +121,20 @@ int32_t sb_maha_set_state(sb_maha_t* h, const double* h_mean, const double* h_C,
  * warm-up gate opened (-1: never) - diagnostics. */
 int32_t sb_maha_last_batch_sums(sb_maha_t* h, int64_t* n_flagged, double* score_sum, int64_t* gate_row,
                                 uintptr_t stream);
+/* with SB_OPT_PROFILE: device time in ms of the last batch's { pass-1 statistics kernel, eigensolver,
+ * prefix/start-inverse kernels, scoring (chain) kernel }.  Synchronises the stream. */
+int32_t sb_maha_kernel_times(sb_maha_t* h, float* out_ms4, uintptr_t stream);
 /* diagnostics: out8 = { first open sub-segment, gate row, flagged rows, Jacobi sweeps, batch rows,
  * sub-segments, sub-segment length, 0 } of the last batch.  Synchronises. */
 int32_t sb_maha_debug_counters(sb_maha_t* h, int64_t* out8, uintptr_t stream);
 /* top-k eigenvectors of the last batch, d x k row-major (diagnostics / subspace parity tests) */
 int32_t sb_maha_get_eigvecs(sb_maha_t* h, double* h_V, uintptr_t stream);
 /* tuning knobs: SB_OPT_GRAM_TERMS 1|3 (TF32 products per Gram element, default 3),
- * SB_OPT_FORCE_GENERIC 0|1 (skip the d=64 tensor-core kernels) */
+ * SB_OPT_FORCE_GENERIC 0|1 (skip the d=64 tensor-core kernels), SB_OPT_PROFILE 0|1 (record CUDA events around
+ * the main kernels on the caller's stream) */
 #define SB_OPT_GRAM_TERMS 1
 #define SB_OPT_FORCE_GENERIC 2
+#define SB_OPT_PROFILE 3
 int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t value);
 /* number of kernel launches issued through this handle so far (bench.py's gpu_launches) */
 int64_t sb_launch_count(void);

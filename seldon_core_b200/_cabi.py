@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsb200.so")
 
 SB_F32, SB_I32 = 0, 1
-SB_OPT_GRAM_TERMS, SB_OPT_FORCE_GENERIC = 1, 2
+SB_OPT_GRAM_TERMS, SB_OPT_FORCE_GENERIC, SB_OPT_PROFILE = 1, 2, 3
 SB_ROUTER_EPSILON_GREEDY, SB_ROUTER_THOMPSON = 0, 1
 SB_REWARD_PER_CALL, SB_REWARD_TABLE, SB_REWARD_BERNOULLI = 0, 1, 2
 
@@ -43,6 +43,7 @@ SIGNATURES = {
     "sb_maha_get_state": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int32), POINTER(c_int32), _uintptr]),
     "sb_maha_set_state": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, _uintptr]),
     "sb_maha_last_batch_sums": (c_int32, [c_void_p, POINTER(c_int64), POINTER(c_double), POINTER(c_int64), _uintptr]),
+    "sb_maha_kernel_times": (c_int32, [c_void_p, c_void_p, _uintptr]),
     "sb_maha_debug_counters": (c_int32, [c_void_p, c_void_p, _uintptr]),
     "sb_maha_get_eigvecs": (c_int32, [c_void_p, c_void_p, _uintptr]),
     "sb_maha_set_option": (c_int32, [c_void_p, c_int32, c_int64]),

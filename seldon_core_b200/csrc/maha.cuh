@@ -74,7 +74,8 @@ struct sb_maha {
   int use_clip;
   sb::SubLayout lay;
   // options
-  int gram_terms, force_generic;
+  int gram_terms, force_generic, profile;
+  cudaEvent_t ev[8];  // profile: [0,1] pass-1 kernel, [2,3] eigh, [4,5] prefix kernels, [6,7] chain kernel
   // device state
   double *d_mean, *d_C, *d_lo, *d_hi;      // committed
   double *d_mean1, *d_C1, *d_lo1, *d_hi1;  // pending (this batch)

@@ -115,18 +115,16 @@ jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, doub
 int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
   const int d = h->d;
   const size_t need = 2 * (size_t)d * d * sizeof(double);
+  if (h->profile) cudaEventRecord(h->ev[2], st);
   if (need <= 200 * 1024) {
-    static bool attr_set = false;
-    if (!attr_set) {
-      SB_CUDA(cudaFuncSetAttribute(jacobi_topk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      attr_set = true;
-    }
+    SB_CUDA(cudaFuncSetAttribute(jacobi_topk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     jacobi_topk<true><<<1, 1024, need, st>>>(h->d_C1, d, h->k, h->KP, nullptr, nullptr, h->d_V, h->d_Vf, h->d_evals,
                                             h->d_gate);
   } else {
     jacobi_topk<false><<<1, 1024, 0, st>>>(h->d_C1, d, h->k, h->KP, ws.eig_W, ws.eig_V, h->d_V, h->d_Vf, h->d_evals,
                                            h->d_gate);
   }
+  if (h->profile) cudaEventRecord(h->ev[3], st);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }

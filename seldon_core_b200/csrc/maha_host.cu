@@ -117,6 +117,8 @@ extern "C" int32_t sb_maha_create(sb_maha_t** out, int32_t d, int32_t n_componen
 
 extern "C" int32_t sb_maha_destroy(sb_maha_t* h) {
   if (!h) return SB_OK;
+  if (h->profile)
+    for (int i = 0; i < 8; ++i) cudaEventDestroy(h->ev[i]);
   cudaFree(h->d_mean);
   cudaFree(h->d_gate);
   delete h;
@@ -138,6 +140,10 @@ extern "C" int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t valu
     h->gram_terms = (int)value;
   } else if (option == SB_OPT_FORCE_GENERIC) {
     h->force_generic = value != 0;
+  } else if (option == SB_OPT_PROFILE) {
+    if (value && !h->profile)
+      for (int i = 0; i < 8; ++i) SB_CUDA(cudaEventCreate(&h->ev[i]));
+    h->profile = value != 0;
   } else {
     set_error("sb_maha_set_option: unknown option %d", option);
     return SB_ERR_INVALID;
@@ -287,6 +293,14 @@ extern "C" int32_t sb_maha_last_batch_sums(sb_maha_t* h, int64_t* n_flagged, dou
   if (n_flagged) *n_flagged = g[2];
   if (score_sum) *score_sum = s;
   if (gate_row) *gate_row = g[1] == LLONG_MAX ? -1 : g[1];
+  return SB_OK;
+}
+
+extern "C" int32_t sb_maha_kernel_times(sb_maha_t* h, float* out_ms4, uintptr_t stream) {
+  SB_REQUIRE(h && out_ms4, SB_ERR_INVALID, "sb_maha_kernel_times: bad arguments");
+  SB_REQUIRE(h->profile, SB_ERR_STATE, "sb_maha_kernel_times: enable SB_OPT_PROFILE first");
+  SB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  for (int i = 0; i < 4; ++i) SB_CUDA(cudaEventElapsedTime(&out_ms4[i], h->ev[2 * i], h->ev[2 * i + 1]));
   return SB_OK;
 }
 

@@ -738,6 +738,7 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
   const int d = h->d, nsub = h->lay.nsub;
   const int KQ = KP + KP * KP;
   const size_t PS = (size_t)d + (size_t)d * d;
+  if (h->profile) cudaEventRecord(h->ev[4], st);
   SB_CUDA(cudaFuncSetAttribute(project_cov, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxD * kMaxKP * 8));
   project_cov<<<1, 256, (size_t)d * KP * sizeof(double), st>>>(h->d_C, h->d_V, d, KP, h->d_PC0);
   SB_LAUNCH_CHECK();
@@ -752,6 +753,7 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
                                                        (long long)h->row0, ws.sub_P, ws.sub_Z, ws.sub_flags);
   SB_LAUNCH_CHECK();
   gate_init<<<1, 32, 0, st>>>(ws.sub_flags, h->lay, (long long)h->row0, h->d_gate, h->d_score_sum);
+  if (h->profile) cudaEventRecord(h->ev[5], st);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }
@@ -780,6 +782,7 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
     SB_LAUNCH_CHECK();
   }
   const bool fast = KP == 16 && d == 64 && !h->force_generic && (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
+  if (h->profile) cudaEventRecord(h->ev[6], st);
   if (fast) {
     int grid = (int)ceil_div(nsub, 8);
     if (grid > kNumSMs * 3) grid = kNumSMs * 3;
@@ -809,6 +812,7 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
                                                      score, flag);
     }
   }
+  if (h->profile) cudaEventRecord(h->ev[7], st);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }

@@ -325,6 +325,7 @@ int launch_pass1(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws,
   const SubLayout& L = h->lay;
   if (L.nsub == 0) return SB_OK;
   const bool fast = h->d == 64 && !h->force_generic && (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
+  if (h->profile) cudaEventRecord(h->ev[0], st);
   if (fast) {
     int grid = (int)ceil_div(L.nsub, 8);
     if (grid > kNumSMs) grid = kNumSMs;
@@ -347,6 +348,7 @@ int launch_pass1(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws,
     else
       pass1_generic<false><<<grid, 256, smem, st>>>(X, ld, h->d, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials);
   }
+  if (h->profile) cudaEventRecord(h->ev[1], st);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }
