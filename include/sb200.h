@@ -109,6 +109,19 @@ int32_t sb_maha_abort_batch(sb_maha_t* h);
 int32_t sb_maha_batch(sb_maha_t* h, const float* d_X, int64_t rows, int64_t ld, float* d_score, int32_t* d_flag,
                       void* d_ws, uint64_t ws_bytes, uintptr_t stream);
 
+/* Pass-1 statistics without any workspace: count, sum and Gram of (x - shift) over `rows` rows of an fp32 device
+ * matrix into d_stats_out (1 + d + d*d doubles, the record layout of sb_maha_pass1_stats).  Has no counterpart in
+ * the reference (which never leaves the host).  It exists for callers that cannot allocate device memory: bindings
+ * with no device allocator of their own (a JNI/cgo shim has no caching allocator to carve a workspace from) and
+ * serving threads that must keep cudaMalloc - a device-wide synchronisation - off the request path.  The
+ * sub-segment partials live in a static device array inside the library (4 259 840 bytes per GPU, held until exit),
+ * hence the limits d <= 64 and rows <= 1 048 576; larger arguments are rejected with SB_ERR_INVALID.  The function
+ * calls no allocating routine.  The array is shared by every call on a GPU: nothing needs clearing between calls,
+ * but calls that overlap on the same GPU race - keep them on one stream.  The first call on each device resolves the
+ * array's device address; make it before starting any stream capture.  d_shift: d floats on the device. */
+int32_t sb_gram_stats_noalloc(const float* d_X, int64_t rows, int32_t d, int64_t ld, const float* d_shift,
+                              double* d_stats_out, uintptr_t stream);
+
 /* Synchronising accessors (public attributes of the reference class / pickling, persistence.py:84).
  * Any h_* pointer may be NULL.  h_C is d*d row-major; has_state = 0 while mean/C are still the scalar 0 of
  * L35-36; has_clip = 0 while clip is None. */

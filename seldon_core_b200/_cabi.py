@@ -40,6 +40,7 @@ SIGNATURES = {
     "sb_maha_commit": (c_int32, [c_void_p, _uintptr]),
     "sb_maha_abort_batch": (c_int32, [c_void_p]),
     "sb_maha_batch": (c_int32, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_uint64, _uintptr]),
+    "sb_gram_stats_noalloc": (c_int32, [c_void_p, c_int64, c_int32, c_int64, c_void_p, c_void_p, _uintptr]),
     "sb_maha_get_state": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int32), POINTER(c_int32), _uintptr]),
     "sb_maha_set_state": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, _uintptr]),
     "sb_maha_last_batch_sums": (c_int32, [c_void_p, POINTER(c_int64), POINTER(c_double), POINTER(c_int64), _uintptr]),

@@ -369,4 +369,90 @@ int launch_finalize_cov(sb_maha* h, const double* all_stats, int nranks, int ran
   return SB_OK;
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// sb_gram_stats_noalloc: the pass-1 statistics for callers that cannot hand over (or create) a device workspace.
+//
+// Who that is: (1) thin bindings that have no device allocator of their own - a JNI or cgo shim around the engine's
+// combiner/transformer units only maps the request matrix and an output record, there is no torch caching allocator
+// behind it to carve the sub-segment partials from; (2) request threads of a serving process that must keep
+// cudaMalloc/cudaFree off the request path, because those calls synchronise the whole device and stall every other
+// request stream.  For them the scratch that sb_maha_pass1_stats takes from the caller lives here, in a file-scope
+// device array that every GPU loading this library carries until the process exits.
+//
+// Limits (both checked, SB_ERR_INVALID otherwise): d <= 64 features and rows <= 1 048 576 per call, i.e. at most
+// 256 sub-segment partials of 64 + 64*64 floats = 4 259 840 bytes of static device memory per GPU.
+//
+// Sharing rules: there is one array per GPU and every call on that GPU uses it.  Nothing has to be cleared between
+// calls - the statistics kernels store (never accumulate into) every slot that the reduction afterwards reads, so
+// whatever the previous call left behind is overwritten before it is looked at - but two calls that overlap on the
+// same GPU (different streams, or different host threads) race on the array; serialise them on one stream.
+// The first call on a device looks up the array's device address; make that first call outside any stream capture.
+namespace {
+
+constexpr int kNoAllocMaxD = 64;
+constexpr int kNoAllocMaxSub = 256;
+constexpr int64_t kNoAllocMaxRows = (int64_t)kNoAllocMaxSub * kMaxSubLen;  // 1 048 576
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) float g_noalloc_partials[(size_t)kNoAllocMaxSub * (kNoAllocMaxD + kNoAllocMaxD * kNoAllocMaxD)];
+
+// In host code `g_noalloc_partials` is only a stand-in for the symbol; the address a kernel can use has to be asked
+// for, once per device, with that device current.
+float* g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};
+
+int noalloc_scratch(float** out) {
+  int dev = -1;
+  SB_CUDA(cudaGetDevice(&dev));
+  SB_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, SB_ERR_INVALID, "sb_gram_stats_noalloc: device ordinal %d not supported", dev);
+  float* p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    void* sym = nullptr;
+    SB_CUDA(cudaGetSymbolAddress(&sym, g_noalloc_partials));
+    p = (float*)sym;
+    __atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return SB_OK;
+}
+
+}  // namespace
 }  // namespace sb
+
+extern "C" int32_t sb_gram_stats_noalloc(const float* d_X, int64_t rows, int32_t d, int64_t ld, const float* d_shift,
+                                         double* d_stats_out, uintptr_t stream) {
+  using namespace sb;
+  SB_REQUIRE(d_X && d_shift && d_stats_out, SB_ERR_INVALID, "sb_gram_stats_noalloc: null pointer");
+  SB_REQUIRE(d >= 1 && d <= kNoAllocMaxD, SB_ERR_INVALID,
+             "sb_gram_stats_noalloc: d=%d exceeds the static scratch limit of %d features", d, kNoAllocMaxD);
+  SB_REQUIRE(rows >= 1 && rows <= kNoAllocMaxRows, SB_ERR_INVALID,
+             "sb_gram_stats_noalloc: rows=%lld outside 1..%lld (static scratch holds %d sub-segment partials); use "
+             "sb_maha_pass1_stats with a caller workspace for larger batches",
+             (long long)rows, (long long)kNoAllocMaxRows, kNoAllocMaxSub);
+  SB_REQUIRE(ld >= d, SB_ERR_INVALID, "sb_gram_stats_noalloc: ld < d");
+  float* scratch = nullptr;
+  int rc = noalloc_scratch(&scratch);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // at most kNoAllocMaxSub sub-segments of equal length (a multiple of 16 rows, at least kMinSubLen)
+  SubLayout L{};
+  L.rows = rows;
+  L.nshort = 0;
+  L.shortlen = kShortLen;
+  int64_t len = ceil_div(ceil_div(rows, kNoAllocMaxSub), 16) * 16;
+  if (len < kMinSubLen) len = kMinSubLen;
+  L.sublen = len;
+  L.nsub = (int32_t)ceil_div(rows, len);
+  const bool fast = d == 64 && (ld % 4 == 0) && (((uintptr_t)d_X & 15) == 0);
+  if (fast) {
+    int grid = (int)ceil_div(L.nsub, 8);
+    pass1_gram64_tf32<false, 3><<<grid, 256, 0, st>>>(d_X, ld, L, d_shift, d_shift, d_shift, scratch);
+  } else {
+    size_t smem = (size_t)kGenRows * ((d + 3) & ~3) * sizeof(float);
+    pass1_generic<false><<<L.nsub, 256, smem, st>>>(d_X, ld, d, L, d_shift, d_shift, d_shift, scratch);
+  }
+  SB_LAUNCH_CHECK();
+  const size_t PS = (size_t)d + (size_t)d * d;
+  reduce_partials<<<(int)ceil_div(PS, 256), 256, 0, st>>>(scratch, L.nsub, d, rows, d_stats_out);
+  SB_LAUNCH_CHECK();
+  return SB_OK;
+}
