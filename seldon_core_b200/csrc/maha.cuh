@@ -46,11 +46,17 @@ struct MahaWs {  // device pointers carved out of the caller's workspace
   double* stats;       // [1 + d + d*d]  this rank's totals
   double* rank_pre;    // [1 + d + d*d]  totals of the ranks before this one
   double* rank_proj;   // [KP + KP*KP]   their projection (offset of every prefix on this rank)
+  double* slices;      // [reduce_slices(d)][d + d*d] stage-1 sums of the partials
+  double* chunk_tot;   // [ceil(nsub/32)][KP + KP*KP] per-chunk totals of the projected partials
+  float* proj_Z;       // [rows][16] clipped projections z (split pass 2, d = 64)
+  float* proj_D;       // [rows][16] y - z, written only for rows with a clipped feature
+  uint8_t* proj_flag;  // [rows] 1 = row has a clipped feature
   double* eig_W;       // [d*d] Jacobi work
   double* eig_V;       // [d*d]
   uint64_t bytes;
 };
 
+int reduce_slices(int d);
 int launch_pass1(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws, cudaStream_t st);
 int launch_reduce(const sb_maha* h, const MahaWs& ws, double* stats_out, cudaStream_t st);
 int launch_finalize_cov(sb_maha* h, const double* all_stats, int nranks, int rank, const MahaWs& ws, cudaStream_t st);
@@ -74,13 +80,15 @@ struct sb_maha {
   int use_clip;
   sb::SubLayout lay;
   // options
-  int gram_terms, force_generic, profile;
+  int gram_terms, force_generic, profile, fused_pass2;
   cudaEvent_t ev[8];  // profile: [0,1] pass-1 kernel, [2,3] eigh, [4,5] prefix kernels, [6,7] chain kernel
   // device state
   double *d_mean, *d_C, *d_lo, *d_hi;      // committed
   double *d_mean1, *d_C1, *d_lo1, *d_hi1;  // pending (this batch)
   float *d_mean_f, *d_lo_f, *d_hi_f;       // fp32 copies of the committed state
   double *d_V, *d_PC0;                     // [d][KP], [KP][KP]
+  double* d_Vfull;                         // [d][d] full Jacobi basis of the previous batch (warm start)
+  int warm_batches;                        // batches since the last cold start of the eigensolver
   float* d_Vf;
   double* d_evals;                 // [KP]
   long long* d_gate;               // [0] b*, [1] i* (global row), [2] n_flagged, [3] eigh sweeps, [4] total rows

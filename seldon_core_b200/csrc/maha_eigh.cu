@@ -25,7 +25,8 @@ __device__ __forceinline__ double warp_sum(double v) {
 template <bool SMEM>
 __global__ void __launch_bounds__(1024, 1)
 jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, double* gV, double* __restrict__ Vd,
-            float* __restrict__ Vf, double* __restrict__ evals, long long* __restrict__ gate) {
+            float* __restrict__ Vf, double* __restrict__ evals, long long* __restrict__ gate,
+            double* __restrict__ Vfull, int warm) {
   extern __shared__ double sm[];
   double* W = SMEM ? sm : gW;
   double* V = SMEM ? sm + (size_t)d * d : gV;
@@ -33,10 +34,25 @@ jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, doub
   __shared__ double norms[kMaxD];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
 
-  for (int idx = tid; idx < d * d; idx += blockDim.x) {
-    int c = idx / d, r = idx - c * d;
-    W[idx] = C[(size_t)r * d + c];  // column c of C (C is symmetric; kept explicit)
-    V[idx] = r == c ? 1.0 : 0.0;
+  if (warm) {
+    // start from the basis of the previous batch: C changes little between batches, so W = C V is already close to
+    // having orthogonal columns and 2-3 sweeps finish the job instead of ~11 from the identity
+    for (int idx = tid; idx < d * d; idx += blockDim.x) V[idx] = Vfull[idx];
+    __syncthreads();
+    for (int idx = tid; idx < d * d; idx += blockDim.x) {
+      const int c = idx / d, r = idx - c * d;
+      const double* crow = C + (size_t)r * d;
+      const double* vcol = V + (size_t)c * d;
+      double acc = 0.0;
+      for (int g = 0; g < d; ++g) acc = fma(crow[g], vcol[g], acc);
+      W[idx] = acc;
+    }
+  } else {
+    for (int idx = tid; idx < d * d; idx += blockDim.x) {
+      int c = idx / d, r = idx - c * d;
+      W[idx] = C[(size_t)r * d + c];  // column c of C (C is symmetric; kept explicit)
+      V[idx] = r == c ? 1.0 : 0.0;
+    }
   }
   const int m = (d + 1) & ~1;  // players in the tournament (one bye if d is odd)
   int sweeps = 0;
@@ -62,9 +78,13 @@ jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, doub
         al = warp_sum(al); be = warp_sum(be); ga = warp_sum(ga);
         if (al == 0.0 || be == 0.0) continue;
         if (fabs(ga) <= 1e-13 * sqrt(al * be)) continue;  // columns orthogonal to working accuracy
-        const double zeta = (be - al) / (2.0 * ga);
-        const double tt = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-        const double cs = 1.0 / sqrt(1.0 + tt * tt), sn = cs * tt;
+        // The rotation only has to be orthogonal to fp64 accuracy (cs^2 + sn^2 = 1); its angle merely sets the
+        // convergence rate, so tan(theta) is computed in fp32 (no fp64 divide / sqrt on the critical path).
+        const float zeta = __fdividef((float)(be - al), (float)(2.0 * ga));
+        const float tf = __fdividef(copysignf(1.f, zeta), fabsf(zeta) + sqrtf(fmaf(zeta, zeta, 1.f)));
+        if (!(fabsf(tf) > 0.f)) continue;  // angle below fp32 resolution (or zeta overflowed): nothing to do
+        const double tt = (double)tf;
+        const double cs = rsqrt(fma(tt, tt, 1.0)), sn = cs * tt;
         double* vp = V + (size_t)p * d;
         double* vq = V + (size_t)q * d;
         for (int r = lane; r < d; r += 32) {
@@ -107,6 +127,7 @@ jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, doub
       }
     }
   }
+  for (int idx = tid; idx < d * d; idx += blockDim.x) Vfull[idx] = V[idx];
   if (tid == 0) gate[3] = sweeps;
 }
 
@@ -115,14 +136,16 @@ jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, doub
 int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
   const int d = h->d;
   const size_t need = 2 * (size_t)d * d * sizeof(double);
+  const int warm = (h->warm_batches % 256) != 0;  // periodic cold start keeps the accumulated basis orthonormal
+  h->warm_batches++;
   if (h->profile) cudaEventRecord(h->ev[2], st);
   if (need <= 200 * 1024) {
     SB_CUDA(cudaFuncSetAttribute(jacobi_topk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     jacobi_topk<true><<<1, 1024, need, st>>>(h->d_C1, d, h->k, h->KP, nullptr, nullptr, h->d_V, h->d_Vf, h->d_evals,
-                                            h->d_gate);
+                                            h->d_gate, h->d_Vfull, warm);
   } else {
     jacobi_topk<false><<<1, 1024, 0, st>>>(h->d_C1, d, h->k, h->KP, ws.eig_W, ws.eig_V, h->d_V, h->d_Vf, h->d_evals,
-                                           h->d_gate);
+                                           h->d_gate, h->d_Vfull, warm);
   }
   if (h->profile) cudaEventRecord(h->ev[3], st);
   SB_LAUNCH_CHECK();

@@ -14,7 +14,7 @@ namespace {
 int padded_k(int k) { return k <= 4 ? 4 : k <= 8 ? 8 : k <= 16 ? 16 : 32; }
 
 // carve the caller's workspace; returns the total number of bytes needed for `nsub_max` sub-segments
-uint64_t carve(const sb_maha* h, int64_t nsub_max, void* base, MahaWs* ws) {
+uint64_t carve(const sb_maha* h, int64_t nsub_max, int64_t rows_max, void* base, MahaWs* ws) {
   const uint64_t d = h->d, KP = h->KP, KQ = KP + KP * KP, PS = d + d * d, SL = 1 + PS;
   uint64_t off = 0;
   auto take = [&](uint64_t bytes) {
@@ -30,6 +30,12 @@ uint64_t carve(const sb_maha* h, int64_t nsub_max, void* base, MahaWs* ws) {
   uint64_t o_st = take(SL * sizeof(double));
   uint64_t o_pre = take(SL * sizeof(double));
   uint64_t o_rp = take(KQ * sizeof(double));
+  uint64_t o_sl = take((uint64_t)reduce_slices((int)d) * PS * sizeof(double));
+  uint64_t o_ct = take((uint64_t)(nsub_max / 32 + 2) * KQ * sizeof(double));
+  const bool split = h->d == 64 && h->KP == 16;
+  uint64_t o_pz = take(split ? (uint64_t)rows_max * 16 * sizeof(float) : 0);
+  uint64_t o_pd = take(split ? (uint64_t)rows_max * 16 * sizeof(float) : 0);
+  uint64_t o_pf = take(split ? (uint64_t)rows_max : 0);
   uint64_t o_W = take(d * d * sizeof(double));
   uint64_t o_V = take(d * d * sizeof(double));
   if (ws) {
@@ -42,6 +48,11 @@ uint64_t carve(const sb_maha* h, int64_t nsub_max, void* base, MahaWs* ws) {
     ws->stats = (double*)(b + o_st);
     ws->rank_pre = (double*)(b + o_pre);
     ws->rank_proj = (double*)(b + o_rp);
+    ws->slices = (double*)(b + o_sl);
+    ws->chunk_tot = (double*)(b + o_ct);
+    ws->proj_Z = (float*)(b + o_pz);
+    ws->proj_D = (float*)(b + o_pd);
+    ws->proj_flag = (uint8_t*)(b + o_pf);
     ws->eig_W = (double*)(b + o_W);
     ws->eig_V = (double*)(b + o_V);
     ws->bytes = off;
@@ -69,7 +80,7 @@ int refresh_float_state(sb_maha* h, cudaStream_t st) {
 int get_ws(const sb_maha* h, int64_t rows, void* d_ws, uint64_t ws_bytes, MahaWs* ws) {
   SB_REQUIRE(d_ws != nullptr && ((uintptr_t)d_ws & 255) == 0, SB_ERR_INVALID, "workspace must be 256-byte aligned");
   const int64_t nsub = make_layout(rows).nsub;
-  uint64_t need = carve(h, nsub, d_ws, ws);
+  uint64_t need = carve(h, nsub, rows, d_ws, ws);
   SB_REQUIRE(need <= ws_bytes, SB_ERR_WORKSPACE, "workspace too small: need %llu bytes, got %llu",
              (unsigned long long)need, (unsigned long long)ws_bytes);
   return SB_OK;
@@ -96,7 +107,7 @@ extern "C" int32_t sb_maha_create(sb_maha_t** out, int32_t d, int32_t n_componen
   h->gram_terms = 3;
   const size_t dd = (size_t)d * d, KP = h->KP;
   double* dbl = nullptr;
-  const size_t n_dbl = 2 * (d + dd + 2 * (size_t)d) + (size_t)d * KP + KP * KP + KP + 1;
+  const size_t n_dbl = 2 * (d + dd + 2 * (size_t)d) + (size_t)d * KP + KP * KP + KP + 1 + dd;
   cudaError_t e = cudaMalloc(&dbl, n_dbl * sizeof(double));
   if (e != cudaSuccess) { set_error("sb_maha_create: cudaMalloc: %s", cudaGetErrorString(e)); delete h; return SB_ERR_CUDA; }
   cudaMemset(dbl, 0, n_dbl * sizeof(double));
@@ -104,6 +115,7 @@ extern "C" int32_t sb_maha_create(sb_maha_t** out, int32_t d, int32_t n_componen
   h->d_mean = p; p += d; h->d_C = p; p += dd; h->d_lo = p; p += d; h->d_hi = p; p += d;
   h->d_mean1 = p; p += d; h->d_C1 = p; p += dd; h->d_lo1 = p; p += d; h->d_hi1 = p; p += d;
   h->d_V = p; p += (size_t)d * KP; h->d_PC0 = p; p += KP * KP; h->d_evals = p; p += KP; h->d_score_sum = p; p += 1;
+  h->d_Vfull = p; p += dd;
   float* flt = nullptr;
   e = cudaMalloc(&flt, (3 * (size_t)d + (size_t)d * KP) * sizeof(float) + 8 * sizeof(long long));
   if (e != cudaSuccess) { set_error("sb_maha_create: cudaMalloc: %s", cudaGetErrorString(e)); cudaFree(dbl); delete h; return SB_ERR_CUDA; }
@@ -127,7 +139,7 @@ extern "C" int32_t sb_maha_destroy(sb_maha_t* h) {
 
 extern "C" int32_t sb_maha_workspace_bytes(const sb_maha_t* h, int64_t max_rows, uint64_t* bytes) {
   SB_REQUIRE(h && bytes && max_rows >= 1, SB_ERR_INVALID, "sb_maha_workspace_bytes: bad arguments");
-  *bytes = carve(h, max_subsegments(max_rows), nullptr, nullptr);
+  *bytes = carve(h, max_subsegments(max_rows), max_rows, nullptr, nullptr);
   return SB_OK;
 }
 
@@ -140,6 +152,8 @@ extern "C" int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t valu
     h->gram_terms = (int)value;
   } else if (option == SB_OPT_FORCE_GENERIC) {
     h->force_generic = value != 0;
+  } else if (option == SB_OPT_FUSED_PASS2) {
+    h->fused_pass2 = value != 0;
   } else if (option == SB_OPT_PROFILE) {
     if (value && !h->profile)
       for (int i = 0; i < 8; ++i) SB_CUDA(cudaEventCreate(&h->ev[i]));
@@ -275,6 +289,7 @@ extern "C" int32_t sb_maha_set_state(sb_maha_t* h, const double* h_mean, const d
     SB_CUDA(cudaMemcpyAsync(h->d_hi, h_clip_hi, d * sizeof(double), cudaMemcpyHostToDevice, st));
   }
   h->n = n; h->has_state = has_state; h->has_clip = has_clip; h->stage = 0;
+  h->warm_batches = 0;
   int rc = refresh_float_state(h, st);
   if (rc) return rc;
   SB_CUDA(cudaStreamSynchronize(st));

@@ -36,83 +36,94 @@ __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync
 
 // -------------------------------------------------------------------------------------------- sub_project
 // out[item][0..KP) = V^T s,  out[item][KP + a*KP + b] = (V^T G V)_ab  for the (s, G) record of each item.
+// fp32 products with fp32 accumulation over <= d terms (the records themselves are fp32-accurate); the prefix sums
+// over sub-segments that follow are fp64.  One CTA per item: G is staged through shared memory in slabs of FC rows
+// (coalesced), T = G V per slab, then V^T T.
 template <typename TIn>
-__global__ void __launch_bounds__(128)
-sub_project(const TIn* __restrict__ recs, size_t rec_stride, int nitems, int d, int KP, const double* __restrict__ V,
+__global__ void __launch_bounds__(256)
+sub_project(const TIn* __restrict__ recs, size_t rec_stride, int nitems, int d, int KP, const float* __restrict__ Vf,
             double* __restrict__ out) {
-  constexpr int FC = 32;
-  __shared__ double Tc[FC * kMaxKP];
+  extern __shared__ __align__(16) float sp_smem[];
+  const int FC = min(d, 8192 / d);           // rows of G per slab (slab <= 32 KB)
+  float* Gs = sp_smem;                        // [FC][d]
+  float* Ts = Gs + (size_t)FC * d;            // [FC][KP]
   const int KQ = KP + KP * KP;
   const int tid = threadIdx.x;
   for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
     const TIn* s = recs + (size_t)item * rec_stride;
     const TIn* G = s + d;
     double* o = out + (size_t)item * KQ;
-    double qacc[8];  // KP*KP <= 1024 = 8 * 128
+    float qacc[4];  // KP*KP <= 1024 = 4 * 256
 #pragma unroll
-    for (int u = 0; u < 8; ++u) qacc[u] = 0.0;
+    for (int u = 0; u < 4; ++u) qacc[u] = 0.f;
     for (int f0 = 0; f0 < d; f0 += FC) {
+      const int nf = min(FC, d - f0);
       __syncthreads();
-      for (int idx = tid; idx < FC * KP; idx += blockDim.x) {
-        const int ff = idx / KP, c = idx - ff * KP, f = f0 + ff;
-        double acc = 0.0;
-        if (f < d) {
-          for (int g = 0; g < d; ++g) {
-            const size_t gi = f <= g ? (size_t)f * d + g : (size_t)g * d + f;  // upper triangle is authoritative
-            acc = fma((double)G[gi], V[(size_t)g * KP + c], acc);
-          }
-        }
-        Tc[idx] = acc;
+      for (int idx = tid; idx < nf * d; idx += blockDim.x) Gs[idx] = (float)G[(size_t)f0 * d + idx];
+      __syncthreads();
+      for (int idx = tid; idx < nf * KP; idx += blockDim.x) {
+        const int ff = idx / KP, c = idx - ff * KP;
+        const float* grow = Gs + (size_t)ff * d;
+        float acc = 0.f;
+        for (int g = 0; g < d; ++g) acc = fmaf(grow[g], __ldg(Vf + (size_t)g * KP + c), acc);
+        Ts[idx] = acc;
       }
       __syncthreads();
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int pq = tid + u * 128;
+      for (int u = 0; u < 4; ++u) {
+        const int pq = tid + u * 256;
         if (pq < KP * KP) {
           const int a = pq / KP, b = pq - a * KP;
-          double acc = qacc[u];
-          for (int ff = 0; ff < FC && f0 + ff < d; ++ff) acc = fma(V[(size_t)(f0 + ff) * KP + a], Tc[ff * KP + b], acc);
+          float acc = qacc[u];
+          for (int ff = 0; ff < nf; ++ff) acc = fmaf(__ldg(Vf + (size_t)(f0 + ff) * KP + a), Ts[ff * KP + b], acc);
           qacc[u] = acc;
         }
       }
     }
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const int pq = tid + u * 128;
-      if (pq < KP * KP) o[KP + pq] = qacc[u];
+    for (int u = 0; u < 4; ++u) {
+      const int pq = tid + u * 256;
+      if (pq < KP * KP) o[KP + pq] = (double)qacc[u];
     }
     if (tid < KP) {
-      double acc = 0.0;
-      for (int f = 0; f < d; ++f) acc = fma((double)s[f], V[(size_t)f * KP + tid], acc);
-      o[tid] = acc;
+      float acc = 0.f;
+      for (int f = 0; f < d; ++f) acc = fmaf((float)s[f], __ldg(Vf + (size_t)f * KP + tid), acc);
+      o[tid] = (double)acc;
     }
   }
 }
 
-// exclusive scan over sub-segments of every projected component, seeded with the rank offset; row nsub = totals
+// Exclusive scan over sub-segments of every projected component, seeded with the rank offset; row nsub = totals.
+// Two kernels, both coalesced over the component index: (1) totals of chunks of 32 sub-segments, (2) every chunk
+// adds up the totals of the chunks before it (a few hundred at most) and rewrites its 32 rows.
+constexpr int kScanChunk = 32;
+
 __global__ void __launch_bounds__(256)
-sub_scan(double* __restrict__ subproj, int nsub, int KQ, const double* __restrict__ rank_off) {
-  const int comp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
-  if (comp >= KQ) return;
-  const int chunk = (nsub + 31) / 32;
-  const int s0 = lane * chunk, s1 = min(nsub, s0 + chunk);
-  double tot = 0.0;
-  for (int s = s0; s < s1; ++s) tot += subproj[(size_t)s * KQ + comp];
-  double incl = tot;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    double up = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += up;
+sub_scan_totals(const double* __restrict__ subproj, int nsub, int KQ, double* __restrict__ chunk_tot) {
+  const int chunk = blockIdx.x;
+  const int s0 = chunk * kScanChunk, s1 = min(nsub, s0 + kScanChunk);
+  for (int comp = threadIdx.x; comp < KQ; comp += blockDim.x) {
+    double acc = 0.0;
+    for (int s = s0; s < s1; ++s) acc += subproj[(size_t)s * KQ + comp];
+    chunk_tot[(size_t)chunk * KQ + comp] = acc;
   }
-  double run = rank_off[comp] + (incl - tot);
-  for (int s = s0; s < s1; ++s) {
-    double v = subproj[(size_t)s * KQ + comp];
-    subproj[(size_t)s * KQ + comp] = run;
-    run += v;
+}
+
+__global__ void __launch_bounds__(256)
+sub_scan_apply(double* __restrict__ subproj, int nsub, int KQ, const double* __restrict__ chunk_tot,
+               const double* __restrict__ rank_off) {
+  const int chunk = blockIdx.x, nchunk = gridDim.x;
+  const int s0 = chunk * kScanChunk, s1 = min(nsub, s0 + kScanChunk);
+  for (int comp = threadIdx.x; comp < KQ; comp += blockDim.x) {
+    double run = rank_off[comp];
+    for (int c = 0; c < chunk; ++c) run += chunk_tot[(size_t)c * KQ + comp];
+    for (int s = s0; s < s1; ++s) {
+      const double v = subproj[(size_t)s * KQ + comp];
+      subproj[(size_t)s * KQ + comp] = run;
+      run += v;
+    }
+    if (chunk == nchunk - 1) subproj[(size_t)nsub * KQ + comp] = run;
   }
-  const double total = __shfl_sync(0xffffffffu, incl, 31) + rank_off[comp];
-  if (lane == 0) subproj[(size_t)nsub * KQ + comp] = total;
 }
 
 // -------------------------------------------------------------------------------------------- sub_start
@@ -526,12 +537,83 @@ __device__ __forceinline__ void mma_m16n8k8_tf32(float (&c)[4], uint32_t a0, uin
 
 constexpr int kZStride = 20;  // floats per projected row in shared memory (16 + pad, keeps float4 alignment)
 
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {  // packed fp32 FMA (FFMA2 on sm_100)
+  unsigned long long ua = *reinterpret_cast<unsigned long long*>(&a), ub = *reinterpret_cast<unsigned long long*>(&b),
+                     uc = *reinterpret_cast<unsigned long long*>(&c), ud;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(ud) : "l"(ua), "l"(ub), "l"(uc));
+  return *reinterpret_cast<float2*>(&ud);
+}
+
+// One row of the chain for a 16-lane group; P = row j of S_i^-1 as 8 packed pairs.  Same algebra as chain_step<16>,
+// with packed FMAs, four independent partial sums for c = S^-1 e, and reciprocals instead of divisions.
+__device__ __forceinline__ float chain_step16(float2 (&P)[8], float& Zrun, float z, float dl, bool need_u, bool active,
+                                              float inv, float w, float nim1, float* buf, int j) {
+  const float e = fmaf(-Zrun, inv, z);
+  const float u = e + dl;
+  buf[j] = e;
+  if (need_u) buf[16 + j] = u;
+  __syncwarp();
+  float2 a0 = make_float2(0.f, 0.f), a1 = a0;
+#pragma unroll
+  for (int i4 = 0; i4 < 4; ++i4) {
+    const float4 ev = *reinterpret_cast<const float4*>(buf + 4 * i4);
+    a0 = ffma2(P[2 * i4], make_float2(ev.x, ev.y), a0);
+    a1 = ffma2(P[2 * i4 + 1], make_float2(ev.z, ev.w), a1);
+  }
+  const float c = (a0.x + a0.y) + (a1.x + a1.y);
+  const float t = group_sum<16>(e * c);
+  float q = t;
+  if (need_u) {  // warp-uniform
+    float2 b0 = make_float2(0.f, 0.f), b1 = b0;
+#pragma unroll
+    for (int i4 = 0; i4 < 4; ++i4) {
+      const float4 uv = *reinterpret_cast<const float4*>(buf + 16 + 4 * i4);
+      b0 = ffma2(P[2 * i4], make_float2(uv.x, uv.y), b0);
+      b1 = ffma2(P[2 * i4 + 1], make_float2(uv.z, uv.w), b1);
+    }
+    q = group_sum<16>(u * ((b0.x + b0.y) + (b1.x + b1.y)));
+  }
+  buf[32 + j] = c;
+  __syncwarp();
+  const float gc = active ? __fdividef(w * c, fmaf(w, t, 1.f)) : 0.f;
+  const float2 ngc = make_float2(-gc, -gc);
+#pragma unroll
+  for (int i4 = 0; i4 < 4; ++i4) {
+    const float4 cv = *reinterpret_cast<const float4*>(buf + 32 + 4 * i4);
+    P[2 * i4] = ffma2(ngc, make_float2(cv.x, cv.y), P[2 * i4]);
+    P[2 * i4 + 1] = ffma2(ngc, make_float2(cv.z, cv.w), P[2 * i4 + 1]);
+  }
+  if (active) Zrun += z;
+  return nim1 * q;
+}
+
+struct BlockPos {  // the 16-row block a group works on
+  int sub;
+  int64_t r, r_end;
+};
+
+// next block of the same sub-segment, or the first block of the next sub-segment assigned to this group
+__device__ __forceinline__ BlockPos next_block(BlockPos p, int stride, const SubLayout& lay, int bstar,
+                                               const int32_t* __restrict__ sub_flags) {
+  p.r += 16;
+  while (p.sub < lay.nsub && p.r >= p.r_end) {
+    p.sub += stride;
+    if (p.sub >= lay.nsub) break;
+    if (p.sub < bstar || !(sub_flags[p.sub] & SUBFLAG_WELL)) continue;  // handled by score_slow
+    p.r = sub_begin(lay, p.sub);
+    p.r_end = sub_begin(lay, p.sub + 1);
+  }
+  return p;
+}
+
 // A warp holds two groups of 16 lanes = two sub-segments.  Per step each group's next 16 rows are projected by the
-// whole warp (M=16 rows, K=64 features, N=16 components; lane (g,t) loads columns 16q+4t..+3 of rows g and g+8, so
-// every warp load covers 64 contiguous bytes of 8 rows), the projections go to shared memory, then both groups walk
-// their 16 rows with chain_step.
+// whole warp on mma.sync TF32 (M=16 rows, K=64 features, N=16 components, 3xTF32 split; lane (g,t) loads columns
+// 16q+4t..+3 of rows g and g+8, so every warp load covers 64 contiguous bytes of 8 rows), the clipped projections z
+// go to shared memory, the correction y - z = V^T(x - clip(x)) is added sparsely (only clipped elements contribute,
+// exact fp32, shared-memory atomics), the next block's rows are prefetched into registers, and then both groups walk
+// their 16 rows with chain_step16.
 template <bool CLIP>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 3)
 score_chain64(const float* __restrict__ X, int64_t ld, SubLayout lay, const float* __restrict__ mean_f,
               const float* __restrict__ lo_f, const float* __restrict__ hi_f, const float* __restrict__ Vf,
               const float* __restrict__ sub_P, const float* __restrict__ sub_Z, const int32_t* __restrict__ sub_flags,
@@ -539,10 +621,15 @@ score_chain64(const float* __restrict__ X, int64_t ld, SubLayout lay, const floa
               double* __restrict__ score_sum, float* __restrict__ score, int32_t* __restrict__ flag) {
   constexpr int KP = 16, D = 64;
   __shared__ __align__(16) float ms[D], los[D], his[D];
-  __shared__ __align__(16) float zbuf[4][2][16 * kZStride];  // [warp][group][row][comp]  clipped projection z
-  __shared__ __align__(16) float dbuf[4][2][16 * kZStride];  // y - z
-  __shared__ int clipf[4][2][16];
+  __shared__ __align__(16) float Vs[CLIP ? D * KP : 4];       // fp32 eigenvectors for the sparse clip correction
+  __shared__ __align__(16) uint4 vfrag[16 * 32];               // B fragments {hi(k=t), hi(k=t+4), lo(k=t), lo(k=t+4)}
+  __shared__ __align__(16) float zbuf[4][2][16 * kZStride];    // [warp][group][row][comp]  z = V^T(clip(x) - a)
+  __shared__ __align__(16) float dbuf[4][2][16 * kZStride];    // y - z, non-zero only on clipped rows
+  __shared__ __align__(16) float4 rowsc[4][2][16];             // per row: 1/(n+i), (n+i)/(n+i+1), n+i-1, clipped?
   __shared__ __align__(16) float cbufs[8][3 * KP];
+  constexpr int kEvCap = 48;                                   // clipped elements listed per block and group
+  __shared__ __align__(16) float2 evlist[4][2][CLIP ? kEvCap : 1];  // {row*64 + col as int bits, x - clip(x)}
+  __shared__ int evcnt[4][2];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
   const int j = lane & 15, grp = lane >> 4;
@@ -551,33 +638,59 @@ score_chain64(const float* __restrict__ X, int64_t ld, SubLayout lay, const floa
     los[f] = CLIP ? lo_f[f] : 0.f;
     his[f] = CLIP ? hi_f[f] : 0.f;
   }
-  // V fragments (constant for the whole batch): step ks uses physical rows 16q+4t+e0 (k=t) and +1 (k=t+4)
-  uint32_t vb[8][2][2], vs[8][2][2];
-#pragma unroll
-  for (int ks = 0; ks < 8; ++ks) {
-    const int f0 = 16 * (ks >> 1) + 4 * t + 2 * (ks & 1);
-#pragma unroll
-    for (int nt = 0; nt < 2; ++nt) {
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const float v = Vf[(f0 + h) * KP + 8 * nt + g];
-        vb[ks][nt][h] = to_tf32(v);
-        vs[ks][nt][h] = to_tf32(v - __uint_as_float(vb[ks][nt][h]));
-      }
-    }
+  if (CLIP)
+    for (int idx = threadIdx.x; idx < D * KP; idx += blockDim.x) Vs[idx] = Vf[idx];
+  for (int idx = threadIdx.x; idx < 16 * 32; idx += blockDim.x) {
+    const int fr = idx >> 5, ln = idx & 31, ks = fr >> 1, nt = fr & 1, gg = ln >> 2, tt = ln & 3;
+    const int f0 = 16 * (ks >> 1) + 4 * tt + 2 * (ks & 1);  // step ks uses physical rows f0 (k=t) and f0+1 (k=t+4)
+    const float v0 = Vf[f0 * KP + 8 * nt + gg], v1 = Vf[(f0 + 1) * KP + 8 * nt + gg];
+    uint4 fr4;
+    fr4.x = to_tf32(v0);
+    fr4.y = to_tf32(v1);
+    fr4.z = to_tf32(v0 - __uint_as_float(fr4.x));
+    fr4.w = to_tf32(v1 - __uint_as_float(fr4.y));
+    vfrag[idx] = fr4;
   }
+  for (int idx = threadIdx.x; idx < 4 * 2 * 16 * kZStride; idx += blockDim.x) (&dbuf[0][0][0])[idx] = 0.f;
+  for (int idx = threadIdx.x; idx < 4 * 2 * 16; idx += blockDim.x) (&rowsc[0][0][0])[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (threadIdx.x < 8) (&evcnt[0][0])[threadIdx.x] = 0;
   __syncthreads();
   float* buf = cbufs[warp * 2 + grp];
   const int groups_total = gridDim.x * 8;
   const int gid = blockIdx.x * 8 + warp * 2 + grp;
   const int bstar = (int)gate[0];
 
-  float P[KP];
+  float2 P[8];
 #pragma unroll
-  for (int i = 0; i < KP; ++i) P[i] = 0.f;
+  for (int i = 0; i < 8; ++i) P[i] = make_float2(0.f, 0.f);
   float Zrun = 0.f;
-  GroupCursor cur{gid - groups_total, 0, 0};
-  cursor_advance<KP>(cur, groups_total, lay, bstar, sub_flags, sub_P, sub_Z, P, Zrun, j);
+  BlockPos cur{gid - groups_total, 0, 0};
+  cur.r = -16;  // next_block() adds 16 first
+  cur = next_block(cur, groups_total, lay, bstar, sub_flags);
+  int loaded_sub = -1;
+
+  float4 xa[2][4], xb[2][4];  // rows g and g+8 of each group's current block
+  auto load_rows = [&](const BlockPos& p) {
+#pragma unroll
+    for (int gs = 0; gs < 2; ++gs) {
+      const int src = gs * 16;
+      const int64_t rb = __shfl_sync(0xffffffffu, p.r, src);
+      const int64_t re = __shfl_sync(0xffffffffu, p.r_end, src);
+      const int psub = __shfl_sync(0xffffffffu, p.sub, src);
+      const bool ghave = psub < lay.nsub;
+      const bool va = ghave && rb + g < re, vb8 = ghave && rb + g + 8 < re;
+      const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4* pa = reinterpret_cast<const float4*>(X + (rb + g) * ld);
+      const float4* pb = reinterpret_cast<const float4*>(X + (rb + g + 8) * ld);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        xa[gs][q] = va ? ldg_stream_f4(pa + 4 * q + t) : zero4;
+        xb[gs][q] = vb8 ? ldg_stream_f4(pb + 4 * q + t) : zero4;
+      }
+    }
+  };
+  load_rows(cur);
+
   long long nf = 0;
   double ss = 0.0;
   while (__any_sync(0xffffffffu, cur.sub < lay.nsub)) {
@@ -585,111 +698,417 @@ score_chain64(const float* __restrict__ X, int64_t ld, SubLayout lay, const floa
     // ---- projection of both groups' blocks by the whole warp
 #pragma unroll
     for (int gs = 0; gs < 2; ++gs) {
-      const int src = gs * 16;  // any lane of group gs knows its cursor
+      const int src = gs * 16;
       const int64_t rb = __shfl_sync(0xffffffffu, cur.r, src);
       const int64_t re = __shfl_sync(0xffffffffu, cur.r_end, src);
       const bool ghave = __shfl_sync(0xffffffffu, (int)have, src) != 0;
       if (!ghave) continue;  // warp-uniform
       const bool va = rb + g < re, vb8 = rb + g + 8 < re;
-      float4 xa[4], xb[4];
-      const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-      const float4* pa = reinterpret_cast<const float4*>(X + (rb + g) * ld);
-      const float4* pb = reinterpret_cast<const float4*>(X + (rb + g + 8) * ld);
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        xa[q] = va ? ldg_stream_f4(pa + 4 * q + t) : zero4;
-        xb[q] = vb8 ? ldg_stream_f4(pb + 4 * q + t) : zero4;
-      }
-      float accz[2][4], accy[2][4];
+      float accz[2][4];
 #pragma unroll
       for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
-        for (int e = 0; e < 4; ++e) { accz[nt][e] = 0.f; accy[nt][e] = 0.f; }
-      int clip_a = 0, clip_b = 0;
+        for (int e = 0; e < 4; ++e) accz[nt][e] = 0.f;
+      float* zrow = zbuf[warp][gs];
+      float* drow = dbuf[warp][gs];
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const float4 m4 = *reinterpret_cast<const float4*>(ms + 16 * q + 4 * t);
-        const float4 l4 = *reinterpret_cast<const float4*>(los + 16 * q + 4 * t);
-        const float4 h4 = *reinterpret_cast<const float4*>(his + 16 * q + 4 * t);
-        const float mm[4] = {m4.x, m4.y, m4.z, m4.w}, ll[4] = {l4.x, l4.y, l4.z, l4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w};
-        const float ra[4] = {xa[q].x, xa[q].y, xa[q].z, xa[q].w}, rbv[4] = {xb[q].x, xb[q].y, xb[q].z, xb[q].w};
-        uint32_t zb[2][4], zs[2][4], yb[2][4], ys[2][4];  // [row g / g+8][element]
+        const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
+        float ra[4] = {xa[gs][q].x, xa[gs][q].y, xa[gs][q].z, xa[gs][q].w};
+        float rbv[4] = {xb[gs][q].x, xb[gs][q].y, xb[gs][q].z, xb[gs][q].w};
+        if (CLIP) {
+          const float4 l4 = *reinterpret_cast<const float4*>(los + 16 * q + 4 * t);
+          const float4 h4 = *reinterpret_cast<const float4*>(his + 16 * q + 4 * t);
+          const float ll[4] = {l4.x, l4.y, l4.z, l4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w};
+          float ca[4], cb[4];
+          bool anyc = false;
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
+          for (int e = 0; e < 4; ++e) {
+            ca[e] = fminf(fmaxf(ra[e], ll[e]), hh[e]);
+            cb[e] = fminf(fmaxf(rbv[e], ll[e]), hh[e]);
+            anyc = anyc || (ca[e] != ra[e]) || (cb[e] != rbv[e]);
+          }
+          if (anyc) {  // rare (0.3 % of the elements are clipped): list them, the group adds V^T(x - clip(x)) later
 #pragma unroll
-          for (int rr = 0; rr < 2; ++rr) {
-            const float x = rr == 0 ? ra[e] : rbv[e];
-            const bool valid = rr == 0 ? va : vb8;
-            float xc = x;
-            if (CLIP) xc = fminf(fmaxf(x, ll[e]), hh[e]);
-            if (CLIP && valid && xc != x) { if (rr == 0) clip_a = 1; else clip_b = 1; }
-            const float dz = valid ? xc - mm[e] : 0.f;
-            zb[rr][e] = to_tf32(dz);
-            zs[rr][e] = to_tf32(dz - __uint_as_float(zb[rr][e]));
-            if (CLIP) {
-              const float dy = valid ? x - mm[e] : 0.f;
-              yb[rr][e] = to_tf32(dy);
-              ys[rr][e] = to_tf32(dy - __uint_as_float(yb[rr][e]));
+            for (int e = 0; e < 4; ++e) {
+#pragma unroll
+              for (int rr = 0; rr < 2; ++rr) {
+                const float x = rr == 0 ? ra[e] : rbv[e];
+                const float xc = rr == 0 ? ca[e] : cb[e];
+                if (xc != x && (rr == 0 ? va : vb8)) {
+                  const int row = rr == 0 ? g : g + 8;
+                  const int col = 16 * q + 4 * t + e;
+                  const int slot = atomicAdd(&evcnt[warp][gs], 1);
+                  if (slot < kEvCap) {
+                    evlist[warp][gs][slot] = make_float2(__int_as_float(row * 64 + col), x - xc);
+                  } else {  // list full (a block dense in outliers): add this element's contribution directly
+                    const float diff = x - xc;
+                    const float* vrow = Vs + col * KP;
+                    for (int c = 0; c < KP; ++c) atomicAdd(drow + row * kZStride + c, diff * vrow[c]);
+                    reinterpret_cast<float*>(&rowsc[warp][gs][row])[3] = 1.f;
+                  }
+                }
+              }
             }
           }
+#pragma unroll
+          for (int e = 0; e < 4; ++e) { ra[e] = ca[e]; rbv[e] = cb[e]; }
+        }
+        uint32_t zb[2][4], zs[2][4];  // [row g / g+8][element]: hi and lo TF32 parts of clip(x) - a
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float da = ra[e] - mm[e], db = rbv[e] - mm[e];
+          zb[0][e] = to_tf32(da);
+          zs[0][e] = to_tf32(da - __uint_as_float(zb[0][e]));
+          zb[1][e] = to_tf32(db);
+          zs[1][e] = to_tf32(db - __uint_as_float(zb[1][e]));
         }
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           const int ks = 2 * q + half, e0 = 2 * half;
 #pragma unroll
           for (int nt = 0; nt < 2; ++nt) {
-            mma_m16n8k8_tf32(accz[nt], zs[0][e0], zs[1][e0], zs[0][e0 + 1], zs[1][e0 + 1], vb[ks][nt][0], vb[ks][nt][1]);
-            mma_m16n8k8_tf32(accz[nt], zb[0][e0], zb[1][e0], zb[0][e0 + 1], zb[1][e0 + 1], vs[ks][nt][0], vs[ks][nt][1]);
-            mma_m16n8k8_tf32(accz[nt], zb[0][e0], zb[1][e0], zb[0][e0 + 1], zb[1][e0 + 1], vb[ks][nt][0], vb[ks][nt][1]);
-            if (CLIP) {
-              mma_m16n8k8_tf32(accy[nt], ys[0][e0], ys[1][e0], ys[0][e0 + 1], ys[1][e0 + 1], vb[ks][nt][0], vb[ks][nt][1]);
-              mma_m16n8k8_tf32(accy[nt], yb[0][e0], yb[1][e0], yb[0][e0 + 1], yb[1][e0 + 1], vs[ks][nt][0], vs[ks][nt][1]);
-              mma_m16n8k8_tf32(accy[nt], yb[0][e0], yb[1][e0], yb[0][e0 + 1], yb[1][e0 + 1], vb[ks][nt][0], vb[ks][nt][1]);
-            }
+            const uint4 vf = vfrag[(ks * 2 + nt) * 32 + lane];
+            mma_m16n8k8_tf32(accz[nt], zs[0][e0], zs[1][e0], zs[0][e0 + 1], zs[1][e0 + 1], vf.x, vf.y);
+            mma_m16n8k8_tf32(accz[nt], zb[0][e0], zb[1][e0], zb[0][e0 + 1], zb[1][e0 + 1], vf.z, vf.w);
+            mma_m16n8k8_tf32(accz[nt], zb[0][e0], zb[1][e0], zb[0][e0 + 1], zb[1][e0 + 1], vf.x, vf.y);
           }
         }
       }
-      float* zrow = zbuf[warp][gs];
-      float* drow = dbuf[warp][gs];
 #pragma unroll
       for (int nt = 0; nt < 2; ++nt) {
         const int c0 = 8 * nt + 2 * t;
         *reinterpret_cast<float2*>(zrow + g * kZStride + c0) = make_float2(accz[nt][0], accz[nt][1]);
         *reinterpret_cast<float2*>(zrow + (g + 8) * kZStride + c0) = make_float2(accz[nt][2], accz[nt][3]);
-        if (CLIP) {
-          *reinterpret_cast<float2*>(drow + g * kZStride + c0) =
-              make_float2(accy[nt][0] - accz[nt][0], accy[nt][1] - accz[nt][1]);
-          *reinterpret_cast<float2*>(drow + (g + 8) * kZStride + c0) =
-              make_float2(accy[nt][2] - accz[nt][2], accy[nt][3] - accz[nt][3]);
-        }
-      }
-      if (CLIP) {
-        clip_a |= __shfl_xor_sync(0xffffffffu, clip_a, 1);
-        clip_a |= __shfl_xor_sync(0xffffffffu, clip_a, 2);
-        clip_b |= __shfl_xor_sync(0xffffffffu, clip_b, 1);
-        clip_b |= __shfl_xor_sync(0xffffffffu, clip_b, 2);
-        if (t == 0) { clipf[warp][gs][g] = clip_a; clipf[warp][gs][g + 8] = clip_b; }
       }
     }
-    __syncwarp();
-    // ---- both groups walk their 16 rows
+    // ---- per-row scalars of this group's block (lane j <-> row j), chain state on entering a sub-segment
     const int64_t rb = cur.r;
+    {
+      const float ni = (float)(double)(n_eff + row0 + rb + j);
+      float* rs = reinterpret_cast<float*>(&rowsc[warp][grp][j]);
+      rs[0] = ni > 0.f ? __fdividef(1.f, ni) : 0.f;
+      rs[1] = __fdividef(ni, ni + 1.f);
+      rs[2] = ni - 1.f;
+    }
+    if (have && cur.sub != loaded_sub) {
+      const float4* src4 = reinterpret_cast<const float4*>(sub_P + (size_t)cur.sub * KP * KP + (size_t)j * KP);
+#pragma unroll
+      for (int i4 = 0; i4 < 4; ++i4) {
+        const float4 v = src4[i4];
+        P[2 * i4] = make_float2(v.x, v.y);
+        P[2 * i4 + 1] = make_float2(v.z, v.w);
+      }
+      Zrun = sub_Z[(size_t)cur.sub * KP + j];
+      loaded_sub = cur.sub;
+    }
+    // ---- prefetch the next block's rows while the chain runs
+    const BlockPos nxt = have ? next_block(cur, groups_total, lay, bstar, sub_flags) : cur;
+    load_rows(nxt);
+    __syncwarp();
     const float* zrow = zbuf[warp][grp];
-    const float* drow = dbuf[warp][grp];
+    float* drow = dbuf[warp][grp];
+    if (CLIP) {
+      // y - z = V^T(x - clip(x)): lane j adds component j of every listed element (exact fp32, one owner per word)
+      const int nev = min(evcnt[warp][grp], kEvCap);  // group-uniform
+      for (int k = 0; k < nev; ++k) {
+        const float2 ev = evlist[warp][grp][k];
+        const int rc = __float_as_int(ev.x), row = rc >> 6, col = rc & 63;
+        drow[row * kZStride + j] = fmaf(ev.y, Vs[col * KP + j], drow[row * kZStride + j]);
+        if (j == 0) reinterpret_cast<float*>(&rowsc[warp][grp][row])[3] = 1.f;
+      }
+      __syncwarp();
+      if (j == 0) evcnt[warp][grp] = 0;
+    }
+    // ---- both groups walk their 16 rows
     float mysc = 0.f;
 #pragma unroll 4
     for (int rr = 0; rr < 16; ++rr) {
       const bool active = have && (rb + rr < cur.r_end);
+      const float4 sc4 = rowsc[warp][grp][rr];
       const float z = active ? zrow[rr * kZStride + j] : 0.f;
       bool clipped = false;
       float dl = 0.f;
       if (CLIP) {
-        clipped = active && clipf[warp][grp][rr] != 0;
-        dl = clipped ? drow[rr * kZStride + j] : 0.f;
+        clipped = sc4.w != 0.f;  // group-uniform
+        if (clipped) {
+          dl = drow[rr * kZStride + j];
+          drow[rr * kZStride + j] = 0.f;  // leave the buffer clean for the next block
+        }
       }
       const bool need_u = CLIP && __any_sync(0xffffffffu, clipped);
-      const float ni = (float)(double)(n_eff + row0 + rb + rr);
-      const float sc = chain_step<KP>(P, Zrun, z, dl, need_u, active, ni, buf, j);
+      const float sc = chain_step16(P, Zrun, z, dl, need_u, active, sc4.x, sc4.y, sc4.z, buf, j);
+      if (j == rr) mysc = sc;
+    }
+    if (CLIP) reinterpret_cast<float*>(&rowsc[warp][grp][j])[3] = 0.f;
+    if (have && rb + j < cur.r_end) {
+      score[rb + j] = mysc;
+      const int f = (double)mysc > threshold;
+      flag[rb + j] = f;
+      nf += f;
+      ss += (double)mysc;
+    }
+    __syncwarp();
+    cur = nxt;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    nf += __shfl_xor_sync(0xffffffffu, nf, o);
+    ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  }
+  if (lane == 0 && (nf != 0 || ss != 0.0)) {
+    atomicAdd((unsigned long long*)(gate + 2), (unsigned long long)nf);
+    atomicAdd(score_sum, ss);
+  }
+}
+
+// ------------------------------------------------------------------ split pass 2 (default for d = 64, k <= 16)
+// The fused kernel above carries the projection's registers (row prefetch, fragments) through the latency-bound
+// chain and ends up with ~9 warps per SM.  Splitting lets each half run at its own occupancy:
+//   project64 : row-independent, streams X once (4*d B/row), writes z (64 B/row), a clip flag (1 B/row) and y - z
+//               for the rows that have a clipped feature (64 B for ~17 % of the rows);
+//   chain16   : lean registers, 16+ warps per SM, reads z back (L2/HBM) and walks the inverse chains.
+// Cost: ~150 B/row of extra DRAM traffic on top of the algorithmic 4*d + 8.
+constexpr int kProjEvCap = 512;   // clipped elements listed per 16-row block; denser blocks take the slow path
+
+template <bool CLIP>
+__global__ void __launch_bounds__(128, 4)
+project64(const float* __restrict__ X, int64_t ld, int64_t rows, const float* __restrict__ mean_f,
+          const float* __restrict__ lo_f, const float* __restrict__ hi_f, const float* __restrict__ Vf,
+          float* __restrict__ Zout, float* __restrict__ Dout, uint8_t* __restrict__ cflag) {
+  constexpr int KP = 16, D = 64;
+  __shared__ __align__(16) float ms[D], los[D], his[D];
+  __shared__ __align__(16) float Vs[CLIP ? D * KP : 4];
+  __shared__ __align__(16) uint4 vfrag[16 * 32];
+  __shared__ __align__(16) float2 evlist[4][CLIP ? kProjEvCap : 1];
+  __shared__ __align__(16) float dtile[4][CLIP ? 16 * KP : 4];
+  __shared__ int evcnt[4];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  for (int f = threadIdx.x; f < D; f += blockDim.x) {
+    ms[f] = mean_f[f];
+    los[f] = CLIP ? lo_f[f] : 0.f;
+    his[f] = CLIP ? hi_f[f] : 0.f;
+  }
+  if (CLIP)
+    for (int idx = threadIdx.x; idx < D * KP; idx += blockDim.x) Vs[idx] = Vf[idx];
+  for (int idx = threadIdx.x; idx < 16 * 32; idx += blockDim.x) {
+    const int fr = idx >> 5, ln = idx & 31, ks = fr >> 1, nt = fr & 1, gg = ln >> 2, tt = ln & 3;
+    const int f0 = 16 * (ks >> 1) + 4 * tt + 2 * (ks & 1);
+    const float v0 = Vf[f0 * KP + 8 * nt + gg], v1 = Vf[(f0 + 1) * KP + 8 * nt + gg];
+    uint4 fr4;
+    fr4.x = to_tf32(v0);
+    fr4.y = to_tf32(v1);
+    fr4.z = to_tf32(v0 - __uint_as_float(fr4.x));
+    fr4.w = to_tf32(v1 - __uint_as_float(fr4.y));
+    vfrag[idx] = fr4;
+  }
+  if (threadIdx.x < 4) evcnt[threadIdx.x] = 0;
+  __syncthreads();
+
+  const int64_t nblocks = (rows + 15) >> 4;
+  const int64_t wstride = (int64_t)gridDim.x * 4;
+  int64_t blk = (int64_t)blockIdx.x * 4 + warp;
+  float4 xa[4], xb[4];
+  auto load_rows = [&](int64_t b) {
+    const int64_t rb = b << 4;
+    const bool va = b < nblocks && rb + g < rows, vb8 = b < nblocks && rb + g + 8 < rows;
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4* pa = reinterpret_cast<const float4*>(X + (rb + g) * ld);
+    const float4* pb = reinterpret_cast<const float4*>(X + (rb + g + 8) * ld);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      xa[q] = va ? ldg_stream_f4(pa + 4 * q + t) : zero4;
+      xb[q] = vb8 ? ldg_stream_f4(pb + 4 * q + t) : zero4;
+    }
+  };
+  load_rows(blk);
+  for (; blk < nblocks; blk += wstride) {
+    const int64_t rb = blk << 4;
+    const bool va = rb + g < rows, vb8 = rb + g + 8 < rows;
+    float accz[2][4];
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) accz[nt][e] = 0.f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 m4 = *reinterpret_cast<const float4*>(ms + 16 * q + 4 * t);
+      const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
+      float ra[4] = {xa[q].x, xa[q].y, xa[q].z, xa[q].w};
+      float rbv[4] = {xb[q].x, xb[q].y, xb[q].z, xb[q].w};
+      if (CLIP) {
+        const float4 l4 = *reinterpret_cast<const float4*>(los + 16 * q + 4 * t);
+        const float4 h4 = *reinterpret_cast<const float4*>(his + 16 * q + 4 * t);
+        const float ll[4] = {l4.x, l4.y, l4.z, l4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w};
+        float ca[4], cb[4];
+        bool anyc = false;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          ca[e] = fminf(fmaxf(ra[e], ll[e]), hh[e]);
+          cb[e] = fminf(fmaxf(rbv[e], ll[e]), hh[e]);
+          anyc = anyc || (ca[e] != ra[e]) || (cb[e] != rbv[e]);
+        }
+        if (anyc) {  // rare: list the clipped elements of this lane
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr) {
+              const float x = rr == 0 ? ra[e] : rbv[e];
+              const float xc = rr == 0 ? ca[e] : cb[e];
+              if (xc != x && (rr == 0 ? va : vb8)) {
+                const int slot = atomicAdd(&evcnt[warp], 1);
+                if (slot < kProjEvCap)
+                  evlist[warp][slot] = make_float2(__int_as_float((rr == 0 ? g : g + 8) * 64 + 16 * q + 4 * t + e), x - xc);
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { ra[e] = ca[e]; rbv[e] = cb[e]; }
+      }
+      uint32_t zb[2][4], zs[2][4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float da = ra[e] - mm[e], db = rbv[e] - mm[e];
+        zb[0][e] = to_tf32(da);
+        zs[0][e] = to_tf32(da - __uint_as_float(zb[0][e]));
+        zb[1][e] = to_tf32(db);
+        zs[1][e] = to_tf32(db - __uint_as_float(zb[1][e]));
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int ks = 2 * q + half, e0 = 2 * half;
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          const uint4 vf = vfrag[(ks * 2 + nt) * 32 + lane];
+          mma_m16n8k8_tf32(accz[nt], zs[0][e0], zs[1][e0], zs[0][e0 + 1], zs[1][e0 + 1], vf.x, vf.y);
+          mma_m16n8k8_tf32(accz[nt], zb[0][e0], zb[1][e0], zb[0][e0 + 1], zb[1][e0 + 1], vf.z, vf.w);
+          mma_m16n8k8_tf32(accz[nt], zb[0][e0], zb[1][e0], zb[0][e0 + 1], zb[1][e0 + 1], vf.x, vf.y);
+        }
+      }
+    }
+    load_rows(blk + wstride);  // next block in flight while this one is written out
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+      const int c0 = 8 * nt + 2 * t;
+      if (va) *reinterpret_cast<float2*>(Zout + (rb + g) * KP + c0) = make_float2(accz[nt][0], accz[nt][1]);
+      if (vb8) *reinterpret_cast<float2*>(Zout + (rb + g + 8) * KP + c0) = make_float2(accz[nt][2], accz[nt][3]);
+    }
+    unsigned rowmask = 0;
+    if (CLIP) {
+      __syncwarp();
+      const int nev = evcnt[warp];  // warp-uniform
+      if (nev > 0) {
+        float* dt = dtile[warp];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) reinterpret_cast<float4*>(dt)[lane + 32 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        __syncwarp();
+        // y - z = V^T(x - clip(x)); the two half-warps take alternate events, lane j adds component j
+        const int half = lane >> 4, jj = lane & 15;
+        if (nev <= kProjEvCap) {
+          for (int k = 0; k < nev; ++k) {
+            const float2 ev = evlist[warp][k];
+            const int rc = __float_as_int(ev.x), row = rc >> 6, col = rc & 63;
+            rowmask |= 1u << row;
+            if ((k & 1) == half) atomicAdd(dt + row * KP + jj, ev.y * Vs[col * KP + jj]);
+          }
+        } else {
+          // more than kProjEvCap clipped elements in 16 rows (degenerate data): recompute the block densely
+          rowmask = 0xffffu;
+          for (int row = half; row < 16; row += 2) {
+            if (rb + row >= rows) break;
+            const float* xr = X + (rb + row) * ld;
+            float acc = 0.f;
+            for (int f = 0; f < D; ++f) {
+              const float x = __ldg(xr + f);
+              acc = fmaf(x - fminf(fmaxf(x, los[f]), his[f]), Vs[f * KP + jj], acc);
+            }
+            dt[row * KP + jj] = acc;
+          }
+        }
+        __syncwarp();
+        for (int row = 0; row < 16; ++row)
+          if ((rowmask >> row) & 1u)
+            if (lane < KP) Dout[(rb + row) * KP + lane] = dt[row * KP + lane];
+        __syncwarp();
+        if (lane == 0) evcnt[warp] = 0;
+      }
+    }
+    if (lane < 16 && rb + lane < rows) cflag[rb + lane] = (uint8_t)((rowmask >> lane) & 1u);
+    __syncwarp();
+  }
+}
+
+// chain over the projected rows: group of 16 lanes per sub-segment, lane j owns row j of S^-1
+template <bool CLIP>
+__global__ void __launch_bounds__(256, CLIP ? 2 : 3)
+chain16(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t* __restrict__ cflag, SubLayout lay,
+        const float* __restrict__ sub_P, const float* __restrict__ sub_Z, const int32_t* __restrict__ sub_flags,
+        long long n_eff, long long row0, double threshold, long long* __restrict__ gate,
+        double* __restrict__ score_sum, float* __restrict__ score, int32_t* __restrict__ flag) {
+  constexpr int KP = 16;
+  __shared__ __align__(16) float4 rowsc[8][2][16];
+  __shared__ __align__(16) float cbufs[16][3 * KP];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int j = lane & 15, grp = lane >> 4;
+  float* buf = cbufs[warp * 2 + grp];
+  const int groups_total = gridDim.x * 16;
+  const int gid = blockIdx.x * 16 + warp * 2 + grp;
+  const int bstar = (int)gate[0];
+
+  float2 P[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) P[i] = make_float2(0.f, 0.f);
+  float Zrun = 0.f;
+  BlockPos cur{gid - groups_total, 0, 0};
+  cur.r = -16;
+  cur = next_block(cur, groups_total, lay, bstar, sub_flags);
+  int loaded_sub = -1;
+  long long nf = 0;
+  double ss = 0.0;
+  while (__any_sync(0xffffffffu, cur.sub < lay.nsub)) {
+    const bool have = cur.sub < lay.nsub;
+    const int64_t rb = cur.r;
+    // this block's 16 projected rows: lane j needs component j of each
+    float zr[16], dr[16];
+    unsigned cmask = 0;
+    if (CLIP) {
+      const bool mine = have && rb + j < cur.r_end && cflag[rb + j] != 0;
+      const unsigned bal = __ballot_sync(0xffffffffu, mine);
+      cmask = (bal >> (16 * grp)) & 0xffffu;
+    }
+#pragma unroll
+    for (int rr = 0; rr < 16; ++rr) {
+      const bool active = have && (rb + rr < cur.r_end);
+      zr[rr] = active ? __ldg(Zp + (rb + rr) * KP + j) : 0.f;
+      dr[rr] = (CLIP && ((cmask >> rr) & 1u)) ? __ldg(Dp + (rb + rr) * KP + j) : 0.f;
+    }
+    {
+      const float ni = (float)(double)(n_eff + row0 + rb + j);
+      rowsc[warp][grp][j] = make_float4(ni > 0.f ? __fdividef(1.f, ni) : 0.f, __fdividef(ni, ni + 1.f), ni - 1.f, 0.f);
+    }
+    if (have && cur.sub != loaded_sub) {
+      const float4* src4 = reinterpret_cast<const float4*>(sub_P + (size_t)cur.sub * KP * KP + (size_t)j * KP);
+#pragma unroll
+      for (int i4 = 0; i4 < 4; ++i4) {
+        const float4 v = src4[i4];
+        P[2 * i4] = make_float2(v.x, v.y);
+        P[2 * i4 + 1] = make_float2(v.z, v.w);
+      }
+      Zrun = sub_Z[(size_t)cur.sub * KP + j];
+      loaded_sub = cur.sub;
+    }
+    __syncwarp();
+    float mysc = 0.f;
+#pragma unroll
+    for (int rr = 0; rr < 16; ++rr) {
+      const bool active = have && (rb + rr < cur.r_end);
+      const float4 sc4 = rowsc[warp][grp][rr];
+      const bool clipped = CLIP && ((cmask >> rr) & 1u);
+      const bool need_u = CLIP && __any_sync(0xffffffffu, clipped);
+      const float sc = chain_step16(P, Zrun, zr[rr], dr[rr], need_u, active, sc4.x, sc4.y, sc4.z, buf, j);
       if (j == rr) mysc = sc;
     }
     if (have && rb + j < cur.r_end) {
@@ -699,9 +1118,8 @@ score_chain64(const float* __restrict__ X, int64_t ld, SubLayout lay, const floa
       nf += f;
       ss += (double)mysc;
     }
-    if (have) cur.r += 16;
     __syncwarp();
-    cursor_advance<KP>(cur, groups_total, lay, bstar, sub_flags, sub_P, sub_Z, P, Zrun, j);
+    if (have) cur = next_block(cur, groups_total, lay, bstar, sub_flags);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -743,11 +1161,16 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
   project_cov<<<1, 256, (size_t)d * KP * sizeof(double), st>>>(h->d_C, h->d_V, d, KP, h->d_PC0);
   SB_LAUNCH_CHECK();
   int grid = nsub < kNumSMs * 8 ? nsub : kNumSMs * 8;
-  sub_project<float><<<grid, 128, 0, st>>>(ws.partials, PS, nsub, d, KP, h->d_V, ws.subproj);
+  const int FC = d < 8192 / d ? d : 8192 / d;
+  const size_t sp_smem = ((size_t)FC * d + (size_t)FC * KP) * sizeof(float);
+  sub_project<float><<<grid, 256, sp_smem, st>>>(ws.partials, PS, nsub, d, KP, h->d_Vf, ws.subproj);
   SB_LAUNCH_CHECK();
-  sub_project<double><<<1, 128, 0, st>>>(ws.rank_pre + 1, PS, 1, d, KP, h->d_V, rank_proj);
+  sub_project<double><<<1, 256, sp_smem, st>>>(ws.rank_pre + 1, PS, 1, d, KP, h->d_Vf, rank_proj);
   SB_LAUNCH_CHECK();
-  sub_scan<<<(int)ceil_div(KQ, 8), 256, 0, st>>>(ws.subproj, nsub, KQ, rank_proj);
+  const int nchunk = (int)ceil_div(nsub, kScanChunk);
+  sub_scan_totals<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
+  SB_LAUNCH_CHECK();
+  sub_scan_apply<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot, rank_proj);
   SB_LAUNCH_CHECK();
   sub_start<KP><<<(int)ceil_div(nsub, 4), 128, 0, st>>>(ws.subproj, h->d_PC0, h->lay, h->k, (long long)h->n_eff,
                                                        (long long)h->row0, ws.sub_P, ws.sub_Z, ws.sub_flags);
@@ -783,7 +1206,28 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
   }
   const bool fast = KP == 16 && d == 64 && !h->force_generic && (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
   if (h->profile) cudaEventRecord(h->ev[6], st);
-  if (fast) {
+  if (fast && !h->fused_pass2) {
+    const int64_t nblocks = ceil_div(h->rows_local, 16);
+    int pgrid = (int)ceil_div(nblocks, 4);
+    if (pgrid > kNumSMs * 4) pgrid = kNumSMs * 4;
+    int cgrid = (int)ceil_div(nsub, 16);
+    if (cgrid > kNumSMs * (h->use_clip ? 2 : 3)) cgrid = kNumSMs * (h->use_clip ? 2 : 3);
+    if (h->use_clip) {
+      project64<true><<<pgrid, 128, 0, st>>>(X, ld, h->rows_local, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf,
+                                            ws.proj_Z, ws.proj_D, ws.proj_flag);
+      SB_LAUNCH_CHECK();
+      chain16<true><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
+                                          (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
+                                          h->d_score_sum, score, flag);
+    } else {
+      project64<false><<<pgrid, 128, 0, st>>>(X, ld, h->rows_local, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf,
+                                             ws.proj_Z, ws.proj_D, ws.proj_flag);
+      SB_LAUNCH_CHECK();
+      chain16<false><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
+                                           (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
+                                           h->d_score_sum, score, flag);
+    }
+  } else if (fast) {
     int grid = (int)ceil_div(nsub, 8);
     if (grid > kNumSMs * 3) grid = kNumSMs * 3;
     if (h->use_clip)

@@ -246,7 +246,9 @@ pass1_generic(const float* __restrict__ X, int64_t ld, int d, SubLayout lay, con
             const int fa = 4 * ta + a, fb = 4 * tb + b;
             if (fa < d && fb < d && fa <= fb) {
               float* p = part + d + (size_t)fa * d + fb;
-              *p = first ? acc[a][b] : *p + acc[a][b];
+              const float v = first ? acc[a][b] : *p + acc[a][b];
+              *p = v;
+              part[d + (size_t)fb * d + fa] = v;  // keep G fully symmetric in memory
             }
           }
       }
@@ -277,6 +279,36 @@ reduce_partials(const float* __restrict__ partials, int nsub, int d, int64_t row
   }
   for (; s < nsub; ++s) acc0 += (double)partials[(size_t)s * PS + src];
   stats[1 + e] = (acc0 + acc1) + (acc2 + acc3);
+}
+
+// Two-stage form for the main path: stage 1 sums a slice of the sub-segments per (element block, slice) CTA into
+// slices[slice][PS]; stage 2 adds the slices in a fixed order (deterministic, no atomics).
+__global__ void __launch_bounds__(256)
+reduce_partials_stage1(const float* __restrict__ partials, int nsub, size_t PS, int nslice, double* __restrict__ slices) {
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= PS) return;
+  const int per = (nsub + nslice - 1) / nslice;
+  const int s0 = blockIdx.y * per, s1 = min(nsub, s0 + per);
+  double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
+  int s = s0;
+  for (; s + 3 < s1; s += 4) {
+    acc0 += (double)partials[(size_t)s * PS + e];
+    acc1 += (double)partials[(size_t)(s + 1) * PS + e];
+    acc2 += (double)partials[(size_t)(s + 2) * PS + e];
+    acc3 += (double)partials[(size_t)(s + 3) * PS + e];
+  }
+  for (; s < s1; ++s) acc0 += (double)partials[(size_t)s * PS + e];
+  slices[(size_t)blockIdx.y * PS + e] = (acc0 + acc1) + (acc2 + acc3);
+}
+
+__global__ void __launch_bounds__(256)
+reduce_partials_stage2(const double* __restrict__ slices, size_t PS, int nslice, int64_t rows, double* __restrict__ stats) {
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e == 0) stats[0] = (double)rows;
+  if (e >= PS) return;
+  double acc = 0.0;
+  for (int k = 0; k < nslice; ++k) acc += slices[(size_t)k * PS + e];
+  stats[1 + e] = acc;
 }
 
 // One thread per covariance element.  all_stats: [nranks][1 + d + d*d].
@@ -353,9 +385,20 @@ int launch_pass1(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws,
   return SB_OK;
 }
 
+int reduce_slices(int d) {
+  const size_t PS = (size_t)d + (size_t)d * d;
+  const int64_t blocks = ceil_div(PS, 256);
+  int64_t n = ceil_div((int64_t)kNumSMs * 8, blocks);
+  return (int)(n < 1 ? 1 : (n > 64 ? 64 : n));
+}
+
 int launch_reduce(const sb_maha* h, const MahaWs& ws, double* stats_out, cudaStream_t st) {
   const size_t PS = (size_t)h->d + (size_t)h->d * h->d;
-  reduce_partials<<<(int)ceil_div(PS, 256), 256, 0, st>>>(ws.partials, h->lay.nsub, h->d, h->rows_local, stats_out);
+  const int nslice = reduce_slices(h->d);
+  dim3 grid((unsigned)ceil_div(PS, 256), (unsigned)nslice);
+  reduce_partials_stage1<<<grid, 256, 0, st>>>(ws.partials, h->lay.nsub, PS, nslice, ws.slices);
+  SB_LAUNCH_CHECK();
+  reduce_partials_stage2<<<(int)ceil_div(PS, 256), 256, 0, st>>>(ws.slices, PS, nslice, h->rows_local, stats_out);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }

@@ -54,14 +54,15 @@ def check_batch(det, ref_score, ref_pred, n_before, k, label):
     return int(err[strict].size)
 
 
-@pytest.mark.parametrize("force_generic", [0, 1])
+@pytest.mark.parametrize("path", ["default", "generic", "fused"])
 @pytest.mark.parametrize("name", CASES)
-def test_reference_fixture(name, force_generic):
+def test_reference_fixture(name, path):
     g, kw, batches = load_case(name)
-    if force_generic and batches[0].shape[1] != 64:
-        pytest.skip("generic path already used for d != 64")
+    if path != "default" and batches[0].shape[1] != 64:
+        pytest.skip("only d = 64 has more than one kernel path")
     det = OutlierMahalanobisB200(**kw)
-    det.set_option(_cabi.SB_OPT_FORCE_GENERIC, force_generic)
+    det.set_option(_cabi.SB_OPT_FORCE_GENERIC, int(path == "generic"))
+    det.set_option(_cabi.SB_OPT_FUSED_PASS2, int(path == "fused"))
     k = min(kw.get("n_components", 3), batches[0].shape[1])
     n = 0
     strict_rows = 0
@@ -92,13 +93,14 @@ def test_projector_matches_scipy_eigh():
     assert projector_err(V, Vref) < TOL
 
 
-@pytest.mark.parametrize("gram_terms", [3, 1])
-def test_c2_shape_primed_then_scored(gram_terms):
+@pytest.mark.parametrize("gram_terms,fused", [(3, 0), (1, 0), (3, 1)])
+def test_c2_shape_primed_then_scored(gram_terms, fused):
     """BASELINE config 2 at a size the oracle finishes in seconds: prime with 40k rows, score 200k x 64, k = 16."""
     prime, _ = synth.maha_rows_numpy(40000, 64, 16, seed=11)
     X, labels = synth.maha_rows_numpy(200000, 64, 16, seed=12)
     det = OutlierMahalanobisB200(n_components=16)
     det.set_option(_cabi.SB_OPT_GRAM_TERMS, gram_terms)
+    det.set_option(_cabi.SB_OPT_FUSED_PASS2, fused)
     ref = MahalanobisLean(n_components=16)
     det.predict(prime, None)
     ref.predict(prime.astype(np.float64), None)
