@@ -210,14 +210,14 @@ def main():
     if rank == 0:
         sampler.start()
     launches0 = L.sb_launch_count()
-    kern_ms = [0.0, 0.0, 0.0, 0.0]
+    kern_ms = [0.0] * 5
     t_host0 = time.perf_counter()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
     import ctypes
 
-    km = (ctypes.c_float * 4)()
+    km = (ctypes.c_float * 5)()
     for _ in range(args.steps):
         step()
     e1.record()
@@ -279,12 +279,20 @@ def main():
         hbm = float(peaks["hbm_gbs"])
         chain_bytes = (4 * D + 8) * rows          # read X once, write score + flag
         pass1_bytes = 4 * D * rows
-        traffic = None
         tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+        pass2_ms = kern_ms[3] + kern_ms[4]
+        # the dominant kernel of the step: pass-1 Gram statistics or pass 2 (projection + chain, one algorithmic unit)
+        if kern_ms[0] >= pass2_ms:
+            dom = {"kernel": "pass1_gram64_tf32 (clip, row sums, 3xTF32 Gram on mma.sync)", "ms": kern_ms[0],
+                   "bytes": pass1_bytes, "traffic_key": "pass1_gram64_dram_bytes_per_launch"}
+        else:
+            dom = {"kernel": "pass 2 = project64 + chain16 (project, inverse chain, score, flag)", "ms": pass2_ms,
+                   "bytes": chain_bytes, "traffic_key": "pass2_dram_bytes_per_launch"}
+        traffic = None
         if os.path.isfile(tpath):
             with open(tpath) as f:
-                traffic = json.load(f).get("score_chain64_dram_bytes_per_launch")
-        chain_gbs = chain_bytes / (kern_ms[3] * 1e-3) / 1e9
+                traffic = json.load(f).get(dom["traffic_key"])
+        dom_gbs = dom["bytes"] / (dom["ms"] * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -295,14 +303,16 @@ def main():
                        "parallelism": "rows sharded over %d rank(s); one all-gather of (count,sum,Gram) per batch"
                                       % world if distributed else "single GPU",
                        "l2": "inputs (%.1f GB per GPU) are larger than L2 (126 MB); no flush needed" % (rows * D * 4 / 1e9)},
-            "roofline": {"bound": "hbm", "kernel": "score_chain64 (pass 2: project, inverse chain, score, flag)",
-                         "achieved": chain_gbs, "peak": hbm, "unit": "GB/s", "frac": chain_gbs / hbm,
+            "roofline": {"bound": "hbm", "kernel": dom["kernel"],
+                         "achieved": dom_gbs, "peak": hbm, "unit": "GB/s", "frac": dom_gbs / hbm,
                          "traffic": traffic, "peak_source": "of " + which,
-                         "algorithmic_bytes_per_launch": chain_bytes,
+                         "algorithmic_bytes_per_launch": dom["bytes"],
                          "kernel_ms": {"pass1_gram": kern_ms[0], "eigh": kern_ms[1], "prefix": kern_ms[2],
-                                       "score_chain": kern_ms[3]},
+                                       "project": kern_ms[3], "chain": kern_ms[4]},
                          "pass1": {"achieved": pass1_bytes / (kern_ms[0] * 1e-3) / 1e9,
                                    "frac": pass1_bytes / (kern_ms[0] * 1e-3) / 1e9 / hbm},
+                         "pass2": {"achieved": chain_bytes / (pass2_ms * 1e-3) / 1e9,
+                                   "frac": chain_bytes / (pass2_ms * 1e-3) / 1e9 / hbm},
                          "whole_batch": {"achieved": (8 * D + 8) * rows / (ms_per_step * 1e-3) / 1e9,
                                          "frac": (8 * D + 8) * rows / (ms_per_step * 1e-3) / 1e9 / hbm}},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks,

@@ -135,8 +135,9 @@ int32_t sb_maha_set_state(sb_maha_t* h, const double* h_mean, const double* h_C,
 int32_t sb_maha_last_batch_sums(sb_maha_t* h, int64_t* n_flagged, double* score_sum, int64_t* gate_row,
                                 uintptr_t stream);
 /* with SB_OPT_PROFILE: device time in ms of the last batch's { pass-1 statistics kernel, eigensolver,
- * prefix/start-inverse kernels, scoring (chain) kernel }.  Synchronises the stream. */
-int32_t sb_maha_kernel_times(sb_maha_t* h, float* out_ms4, uintptr_t stream);
+ * prefix/start-inverse kernels, pass-2 projection kernel (0 when pass 2 runs fused), pass-2 chain kernel }.
+ * Synchronises the stream. */
+int32_t sb_maha_kernel_times(sb_maha_t* h, float* out_ms5, uintptr_t stream);
 /* diagnostics: out8 = { first open sub-segment, gate row, flagged rows, Jacobi sweeps, batch rows,
  * sub-segments, sub-segment length, 0 } of the last batch.  Synchronises. */
 int32_t sb_maha_debug_counters(sb_maha_t* h, int64_t* out8, uintptr_t stream);

@@ -81,7 +81,7 @@ struct sb_maha {
   sb::SubLayout lay;
   // options
   int gram_terms, force_generic, profile, fused_pass2;
-  cudaEvent_t ev[8];  // profile: [0,1] pass-1 kernel, [2,3] eigh, [4,5] prefix kernels, [6,7] chain kernel
+  cudaEvent_t ev[10];  // profile: [0,1] pass-1 kernel, [2,3] eigh, [4,5] prefix kernels, [6,7] projection, [8,9] chain
   // device state
   double *d_mean, *d_C, *d_lo, *d_hi;      // committed
   double *d_mean1, *d_C1, *d_lo1, *d_hi1;  // pending (this batch)

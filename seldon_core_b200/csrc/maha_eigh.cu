@@ -77,14 +77,18 @@ jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, doub
         }
         al = warp_sum(al); be = warp_sum(be); ga = warp_sum(ga);
         if (al == 0.0 || be == 0.0) continue;
-        if (fabs(ga) <= 1e-13 * sqrt(al * be)) continue;  // columns orthogonal to working accuracy
+        if (ga * ga <= 1e-22 * (al * be)) continue;  // |cos| <= 1e-11: columns orthogonal to working accuracy
         // The rotation only has to be orthogonal to fp64 accuracy (cs^2 + sn^2 = 1); its angle merely sets the
         // convergence rate, so tan(theta) is computed in fp32 (no fp64 divide / sqrt on the critical path).
         const float zeta = __fdividef((float)(be - al), (float)(2.0 * ga));
         const float tf = __fdividef(copysignf(1.f, zeta), fabsf(zeta) + sqrtf(fmaf(zeta, zeta, 1.f)));
         if (!(fabsf(tf) > 0.f)) continue;  // angle below fp32 resolution (or zeta overflowed): nothing to do
         const double tt = (double)tf;
-        const double cs = rsqrt(fma(tt, tt, 1.0)), sn = cs * tt;
+        const double hh = fma(tt, tt, 1.0);
+        double cs = (double)rsqrtf((float)hh);            // fp32 seed, two Newton steps -> full fp64 accuracy
+        cs = cs * fma(-0.5 * hh, cs * cs, 1.5);
+        cs = cs * fma(-0.5 * hh, cs * cs, 1.5);
+        const double sn = cs * tt;
         double* vp = V + (size_t)p * d;
         double* vq = V + (size_t)q * d;
         for (int r = lane; r < d; r += 32) {

@@ -117,12 +117,13 @@ extern "C" int32_t sb_maha_create(sb_maha_t** out, int32_t d, int32_t n_componen
   h->d_V = p; p += (size_t)d * KP; h->d_PC0 = p; p += KP * KP; h->d_evals = p; p += KP; h->d_score_sum = p; p += 1;
   h->d_Vfull = p; p += dd;
   float* flt = nullptr;
-  e = cudaMalloc(&flt, (3 * (size_t)d + (size_t)d * KP) * sizeof(float) + 8 * sizeof(long long));
+  const size_t d4 = ((size_t)d + 3) & ~(size_t)3;  // keep every fp32 array 16-byte aligned
+  e = cudaMalloc(&flt, (3 * d4 + (size_t)d * KP) * sizeof(float) + 8 * sizeof(long long));
   if (e != cudaSuccess) { set_error("sb_maha_create: cudaMalloc: %s", cudaGetErrorString(e)); cudaFree(dbl); delete h; return SB_ERR_CUDA; }
-  cudaMemset(flt, 0, (3 * (size_t)d + (size_t)d * KP) * sizeof(float) + 8 * sizeof(long long));
+  cudaMemset(flt, 0, (3 * d4 + (size_t)d * KP) * sizeof(float) + 8 * sizeof(long long));
   h->d_gate = (long long*)flt;  // 8-byte aligned slots first
   float* q = flt + 16;
-  h->d_mean_f = q; q += d; h->d_lo_f = q; q += d; h->d_hi_f = q; q += d; h->d_Vf = q;
+  h->d_mean_f = q; q += d4; h->d_lo_f = q; q += d4; h->d_hi_f = q; q += d4; h->d_Vf = q;
   *out = h;
   return SB_OK;
 }
@@ -130,7 +131,7 @@ extern "C" int32_t sb_maha_create(sb_maha_t** out, int32_t d, int32_t n_componen
 extern "C" int32_t sb_maha_destroy(sb_maha_t* h) {
   if (!h) return SB_OK;
   if (h->profile)
-    for (int i = 0; i < 8; ++i) cudaEventDestroy(h->ev[i]);
+    for (int i = 0; i < 10; ++i) cudaEventDestroy(h->ev[i]);
   cudaFree(h->d_mean);
   cudaFree(h->d_gate);
   delete h;
@@ -156,7 +157,7 @@ extern "C" int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t valu
     h->fused_pass2 = value != 0;
   } else if (option == SB_OPT_PROFILE) {
     if (value && !h->profile)
-      for (int i = 0; i < 8; ++i) SB_CUDA(cudaEventCreate(&h->ev[i]));
+      for (int i = 0; i < 10; ++i) SB_CUDA(cudaEventCreate(&h->ev[i]));
     h->profile = value != 0;
   } else {
     set_error("sb_maha_set_option: unknown option %d", option);
@@ -311,11 +312,11 @@ extern "C" int32_t sb_maha_last_batch_sums(sb_maha_t* h, int64_t* n_flagged, dou
   return SB_OK;
 }
 
-extern "C" int32_t sb_maha_kernel_times(sb_maha_t* h, float* out_ms4, uintptr_t stream) {
-  SB_REQUIRE(h && out_ms4, SB_ERR_INVALID, "sb_maha_kernel_times: bad arguments");
+extern "C" int32_t sb_maha_kernel_times(sb_maha_t* h, float* out_ms5, uintptr_t stream) {
+  SB_REQUIRE(h && out_ms5, SB_ERR_INVALID, "sb_maha_kernel_times: bad arguments");
   SB_REQUIRE(h->profile, SB_ERR_STATE, "sb_maha_kernel_times: enable SB_OPT_PROFILE first");
   SB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
-  for (int i = 0; i < 4; ++i) SB_CUDA(cudaEventElapsedTime(&out_ms4[i], h->ev[2 * i], h->ev[2 * i + 1]));
+  for (int i = 0; i < 5; ++i) SB_CUDA(cudaEventElapsedTime(&out_ms5[i], h->ev[2 * i], h->ev[2 * i + 1]));
   return SB_OK;
 }
 

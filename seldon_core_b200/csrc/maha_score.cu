@@ -46,7 +46,7 @@ sub_project(const TIn* __restrict__ recs, size_t rec_stride, int nitems, int d, 
   extern __shared__ __align__(16) float sp_smem[];
   const int FC = min(d, 8192 / d);           // rows of G per slab (slab <= 32 KB)
   float* Gs = sp_smem;                        // [FC][d]
-  float* Ts = Gs + (size_t)FC * d;            // [FC][KP]
+  float* Ts = Gs + (((size_t)FC * d + 3) & ~(size_t)3);  // [FC][KP], 16-byte aligned
   const int KQ = KP + KP * KP;
   const int tid = threadIdx.x;
   for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
@@ -61,12 +61,22 @@ sub_project(const TIn* __restrict__ recs, size_t rec_stride, int nitems, int d, 
       __syncthreads();
       for (int idx = tid; idx < nf * d; idx += blockDim.x) Gs[idx] = (float)G[(size_t)f0 * d + idx];
       __syncthreads();
-      for (int idx = tid; idx < nf * KP; idx += blockDim.x) {
-        const int ff = idx / KP, c = idx - ff * KP;
+      // T = G V for this slab: each thread owns 4 consecutive components of one row (V rows read as float4)
+      const int KP4 = KP >> 2;
+      for (int idx = tid; idx < nf * KP4; idx += blockDim.x) {
+        const int ff = idx / KP4, c4 = idx - ff * KP4;
         const float* grow = Gs + (size_t)ff * d;
-        float acc = 0.f;
-        for (int g = 0; g < d; ++g) acc = fmaf(grow[g], __ldg(Vf + (size_t)g * KP + c), acc);
-        Ts[idx] = acc;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+        for (int g = 0; g < d; ++g) {
+          const float gv = grow[g];
+          const float4 v = __ldg(reinterpret_cast<const float4*>(Vf + (size_t)g * KP) + c4);
+          acc.x = fmaf(gv, v.x, acc.x);
+          acc.y = fmaf(gv, v.y, acc.y);
+          acc.z = fmaf(gv, v.z, acc.z);
+          acc.w = fmaf(gv, v.w, acc.w);
+        }
+        reinterpret_cast<float4*>(Ts)[idx] = acc;
       }
       __syncthreads();
 #pragma unroll
@@ -1041,21 +1051,31 @@ project64(const float* __restrict__ X, int64_t ld, int64_t rows, const float* __
   }
 }
 
-// chain over the projected rows: group of 16 lanes per sub-segment, lane j owns row j of S^-1
+// chain over the projected rows: group of 16 lanes per sub-segment, lane j owns row j of S^-1.
+// Two rows per step (rank-2 form of the Sherman-Morrison update): with c1 = P e1, d2 = P e2 and the three dot
+// products t11 = e1.c1, t12 = e1.d2, t22 = e2.d2 (one 3-wide shuffle butterfly),
+//     g1 = w1/(1 + w1 t11),  c2 = d2 - g1 t12 c1,  t2 = t22 - g1 t12^2,  g2 = w2/(1 + w2 t2),
+//     P <- P - g1 c1 c1^T - g2 c2 c2^T,   score1 = (n+i-1) t11,  score2 = (n+i) t2
+// (clipped rows use u = e + (y - z) in the quadratic forms: q11 = u1.P u1, score2 = q22 - g1 (c1.u2)^2).
+// All deviations e, u of a 16-row block are formed up front from the running prefix and parked in shared memory,
+// so a step needs a single warp synchronisation (for the c broadcast).
 template <bool CLIP>
-__global__ void __launch_bounds__(256, CLIP ? 2 : 3)
+__global__ void __launch_bounds__(256, 2)
 chain16(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t* __restrict__ cflag, SubLayout lay,
         const float* __restrict__ sub_P, const float* __restrict__ sub_Z, const int32_t* __restrict__ sub_flags,
         long long n_eff, long long row0, double threshold, long long* __restrict__ gate,
         double* __restrict__ score_sum, float* __restrict__ score, int32_t* __restrict__ flag) {
   constexpr int KP = 16;
-  __shared__ __align__(16) float4 rowsc[8][2][16];
-  __shared__ __align__(16) float cbufs[16][3 * KP];
+  __shared__ __align__(16) float4 rowsc[16][16];          // [group in CTA][row]: 1/(n+i), (n+i)/(n+i+1), n+i-1
+  __shared__ __align__(16) float ebuf[16][16 * KP];       // [group][row][comp]  e
+  __shared__ __align__(16) float ubuf[16][CLIP ? 16 * KP : 4];
+  __shared__ __align__(16) float cbufs[16][2][2 * KP];    // [group][parity][c1 | c2]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int j = lane & 15, grp = lane >> 4;
-  float* buf = cbufs[warp * 2 + grp];
+  const int j = lane & 15, grp = lane >> 4, gi = warp * 2 + grp;
+  float* eb = ebuf[gi];
+  float* ub = ubuf[gi];
   const int groups_total = gridDim.x * 16;
-  const int gid = blockIdx.x * 16 + warp * 2 + grp;
+  const int gid = blockIdx.x * 16 + gi;
   const int bstar = (int)gate[0];
 
   float2 P[8];
@@ -1071,23 +1091,22 @@ chain16(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_
   while (__any_sync(0xffffffffu, cur.sub < lay.nsub)) {
     const bool have = cur.sub < lay.nsub;
     const int64_t rb = cur.r;
-    // this block's 16 projected rows: lane j needs component j of each
-    float zr[16], dr[16];
+    const int nact = have ? (int)min((int64_t)16, cur.r_end - rb) : 0;  // active rows of this block
+    float er[16], dr[16];
     unsigned cmask = 0;
     if (CLIP) {
-      const bool mine = have && rb + j < cur.r_end && cflag[rb + j] != 0;
+      const bool mine = j < nact && cflag[rb + j] != 0;
       const unsigned bal = __ballot_sync(0xffffffffu, mine);
       cmask = (bal >> (16 * grp)) & 0xffffu;
     }
 #pragma unroll
     for (int rr = 0; rr < 16; ++rr) {
-      const bool active = have && (rb + rr < cur.r_end);
-      zr[rr] = active ? __ldg(Zp + (rb + rr) * KP + j) : 0.f;
+      er[rr] = rr < nact ? __ldg(Zp + (rb + rr) * KP + j) : 0.f;
       dr[rr] = (CLIP && ((cmask >> rr) & 1u)) ? __ldg(Dp + (rb + rr) * KP + j) : 0.f;
     }
     {
       const float ni = (float)(double)(n_eff + row0 + rb + j);
-      rowsc[warp][grp][j] = make_float4(ni > 0.f ? __fdividef(1.f, ni) : 0.f, __fdividef(ni, ni + 1.f), ni - 1.f, 0.f);
+      rowsc[gi][j] = make_float4(ni > 0.f ? __fdividef(1.f, ni) : 0.f, __fdividef(ni, ni + 1.f), ni - 1.f, 0.f);
     }
     if (have && cur.sub != loaded_sub) {
       const float4* src4 = reinterpret_cast<const float4*>(sub_P + (size_t)cur.sub * KP * KP + (size_t)j * KP);
@@ -1101,17 +1120,93 @@ chain16(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_
       loaded_sub = cur.sub;
     }
     __syncwarp();
-    float mysc = 0.f;
+    // deviations of the whole block from the running prefix: e_i = z_i - Z_i/(n+i), u_i = e_i + (y_i - z_i)
+    const bool any_clip = CLIP && __any_sync(0xffffffffu, cmask != 0);
 #pragma unroll
     for (int rr = 0; rr < 16; ++rr) {
-      const bool active = have && (rb + rr < cur.r_end);
-      const float4 sc4 = rowsc[warp][grp][rr];
-      const bool clipped = CLIP && ((cmask >> rr) & 1u);
-      const bool need_u = CLIP && __any_sync(0xffffffffu, clipped);
-      const float sc = chain_step16(P, Zrun, zr[rr], dr[rr], need_u, active, sc4.x, sc4.y, sc4.z, buf, j);
-      if (j == rr) mysc = sc;
+      const float inv = rowsc[gi][rr].x;
+      const float z = er[rr];
+      const float e = rr < nact ? fmaf(-Zrun, inv, z) : 0.f;
+      Zrun += z;
+      er[rr] = e;
+      eb[rr * KP + j] = e;
+      if (any_clip) ub[rr * KP + j] = e + dr[rr];
     }
-    if (have && rb + j < cur.r_end) {
+    __syncwarp();
+    float mysc = 0.f;
+#pragma unroll
+    for (int pr = 0; pr < 8; ++pr) {
+      const int r1 = 2 * pr, r2 = 2 * pr + 1;
+      const float4 sA = rowsc[gi][r1], sB = rowsc[gi][r2];
+      float2 a0 = make_float2(0.f, 0.f), a1 = a0, b0 = a0, b1 = a0;
+#pragma unroll
+      for (int i4 = 0; i4 < 4; ++i4) {
+        const float4 e1 = *reinterpret_cast<const float4*>(eb + r1 * KP + 4 * i4);
+        const float4 e2 = *reinterpret_cast<const float4*>(eb + r2 * KP + 4 * i4);
+        a0 = ffma2(P[2 * i4], make_float2(e1.x, e1.y), a0);
+        a1 = ffma2(P[2 * i4 + 1], make_float2(e1.z, e1.w), a1);
+        b0 = ffma2(P[2 * i4], make_float2(e2.x, e2.y), b0);
+        b1 = ffma2(P[2 * i4 + 1], make_float2(e2.z, e2.w), b1);
+      }
+      const float c1 = (a0.x + a0.y) + (a1.x + a1.y);
+      const float d2 = (b0.x + b0.y) + (b1.x + b1.y);
+      float t11 = er[r1] * c1, t12 = er[r1] * d2, t22 = er[r2] * d2;
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) {
+        t11 += __shfl_xor_sync(0xffffffffu, t11, o);
+        t12 += __shfl_xor_sync(0xffffffffu, t12, o);
+        t22 += __shfl_xor_sync(0xffffffffu, t22, o);
+      }
+      const float g1 = r1 < nact ? __fdividef(sA.y, fmaf(sA.y, t11, 1.f)) : 0.f;
+      const float k12 = g1 * t12;
+      const float c2 = fmaf(-k12, c1, d2);
+      const float t2 = fmaf(-k12, t12, t22);
+      const float g2 = r2 < nact ? __fdividef(sB.y, fmaf(sB.y, t2, 1.f)) : 0.f;
+      float q1 = t11, q2 = t2;
+      const bool pair_clip = CLIP && __any_sync(0xffffffffu, ((cmask >> r1) & 3u) != 0);
+      if (pair_clip) {  // warp-uniform: quadratic forms with u instead of e
+        float2 v0 = make_float2(0.f, 0.f), v1 = v0, w0 = v0, w1 = v0;
+        const float u1j = ub[r1 * KP + j], u2j = ub[r2 * KP + j];
+#pragma unroll
+        for (int i4 = 0; i4 < 4; ++i4) {
+          const float4 u1 = *reinterpret_cast<const float4*>(ub + r1 * KP + 4 * i4);
+          const float4 u2 = *reinterpret_cast<const float4*>(ub + r2 * KP + 4 * i4);
+          v0 = ffma2(P[2 * i4], make_float2(u1.x, u1.y), v0);
+          v1 = ffma2(P[2 * i4 + 1], make_float2(u1.z, u1.w), v1);
+          w0 = ffma2(P[2 * i4], make_float2(u2.x, u2.y), w0);
+          w1 = ffma2(P[2 * i4 + 1], make_float2(u2.z, u2.w), w1);
+        }
+        float q11 = u1j * ((v0.x + v0.y) + (v1.x + v1.y));
+        float q22 = u2j * ((w0.x + w0.y) + (w1.x + w1.y));
+        float x12 = c1 * u2j;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+          q11 += __shfl_xor_sync(0xffffffffu, q11, o);
+          q22 += __shfl_xor_sync(0xffffffffu, q22, o);
+          x12 += __shfl_xor_sync(0xffffffffu, x12, o);
+        }
+        q1 = q11;
+        q2 = fmaf(-g1 * x12, x12, q22);
+      }
+      if (j == r1) mysc = sA.z * q1;
+      if (j == r2) mysc = sB.z * q2;
+      // broadcast c1, c2 and apply both rank-1 terms to row j of P
+      float* cb = cbufs[gi][pr & 1];
+      cb[j] = c1;
+      cb[KP + j] = c2;
+      __syncwarp();
+      const float2 n1 = make_float2(-g1 * c1, -g1 * c1), n2 = make_float2(-g2 * c2, -g2 * c2);
+#pragma unroll
+      for (int i4 = 0; i4 < 4; ++i4) {
+        const float4 x1 = *reinterpret_cast<const float4*>(cb + 4 * i4);
+        const float4 x2 = *reinterpret_cast<const float4*>(cb + KP + 4 * i4);
+        P[2 * i4] = ffma2(n1, make_float2(x1.x, x1.y), P[2 * i4]);
+        P[2 * i4 + 1] = ffma2(n1, make_float2(x1.z, x1.w), P[2 * i4 + 1]);
+        P[2 * i4] = ffma2(n2, make_float2(x2.x, x2.y), P[2 * i4]);
+        P[2 * i4 + 1] = ffma2(n2, make_float2(x2.z, x2.w), P[2 * i4 + 1]);
+      }
+    }
+    if (j < nact) {
       score[rb + j] = mysc;
       const int f = (double)mysc > threshold;
       flag[rb + j] = f;
@@ -1162,7 +1257,7 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
   SB_LAUNCH_CHECK();
   int grid = nsub < kNumSMs * 8 ? nsub : kNumSMs * 8;
   const int FC = d < 8192 / d ? d : 8192 / d;
-  const size_t sp_smem = ((size_t)FC * d + (size_t)FC * KP) * sizeof(float);
+  const size_t sp_smem = ((((size_t)FC * d + 3) & ~(size_t)3) + (size_t)FC * KP) * sizeof(float);
   sub_project<float><<<grid, 256, sp_smem, st>>>(ws.partials, PS, nsub, d, KP, h->d_Vf, ws.subproj);
   SB_LAUNCH_CHECK();
   sub_project<double><<<1, 256, sp_smem, st>>>(ws.rank_pre + 1, PS, 1, d, KP, h->d_Vf, rank_proj);
@@ -1205,17 +1300,18 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
     SB_LAUNCH_CHECK();
   }
   const bool fast = KP == 16 && d == 64 && !h->force_generic && (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
-  if (h->profile) cudaEventRecord(h->ev[6], st);
+  if (h->profile) { cudaEventRecord(h->ev[6], st); cudaEventRecord(h->ev[7], st); cudaEventRecord(h->ev[8], st); }
   if (fast && !h->fused_pass2) {
     const int64_t nblocks = ceil_div(h->rows_local, 16);
     int pgrid = (int)ceil_div(nblocks, 4);
     if (pgrid > kNumSMs * 4) pgrid = kNumSMs * 4;
     int cgrid = (int)ceil_div(nsub, 16);
-    if (cgrid > kNumSMs * (h->use_clip ? 2 : 3)) cgrid = kNumSMs * (h->use_clip ? 2 : 3);
+    if (cgrid > kNumSMs * 2) cgrid = kNumSMs * 2;
     if (h->use_clip) {
       project64<true><<<pgrid, 128, 0, st>>>(X, ld, h->rows_local, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf,
                                             ws.proj_Z, ws.proj_D, ws.proj_flag);
       SB_LAUNCH_CHECK();
+      if (h->profile) { cudaEventRecord(h->ev[7], st); cudaEventRecord(h->ev[8], st); }
       chain16<true><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
                                           (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
                                           h->d_score_sum, score, flag);
@@ -1223,6 +1319,7 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
       project64<false><<<pgrid, 128, 0, st>>>(X, ld, h->rows_local, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf,
                                              ws.proj_Z, ws.proj_D, ws.proj_flag);
       SB_LAUNCH_CHECK();
+      if (h->profile) { cudaEventRecord(h->ev[7], st); cudaEventRecord(h->ev[8], st); }
       chain16<false><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
                                            (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
                                            h->d_score_sum, score, flag);
@@ -1256,7 +1353,7 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
                                                      score, flag);
     }
   }
-  if (h->profile) cudaEventRecord(h->ev[7], st);
+  if (h->profile) cudaEventRecord(h->ev[9], st);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }
