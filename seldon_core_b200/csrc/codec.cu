@@ -5,6 +5,8 @@
 //   Tensor    : ... 12 <varint 8*count> <count x little-endian f64>      -> the values are one contiguous block
 //   ListValue : per row  0a <varint L1> 32 <varint L2> ( 0a 09 11 <f64> ) x cols   (fixed stride for fixed cols)
 // All four kernels are streaming: 12 B/value for the tensor forms, 11 + 4 (+ header) B/value for ListValue.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -137,6 +139,268 @@ pack_listvalue_kernel(const TIn* __restrict__ in, int64_t rows, int64_t cols, in
   }
 }
 
+// ---- shared-memory staged ListValue kernels -------------------------------------------------------------------
+// A CTA moves a chunk of R rows (R a multiple of 16, so the chunk is a whole number of 16-byte words when the payload
+// base is 16-byte aligned) between global and shared memory with coalesced 16-byte accesses; the 11-byte records are
+// then picked out of / assembled in shared memory with aligned 32-bit words and funnel shifts.
+__device__ __forceinline__ uint32_t smem_u32_at(const uint32_t* w, int byte_off) {  // 4 bytes at any byte offset
+  const int k = byte_off >> 2, sh = (byte_off & 3) * 8;
+  return __funnelshift_r(w[k], w[k + 1], sh);
+}
+
+__global__ void __launch_bounds__(256)
+unpack_listvalue_staged(const uint8_t* __restrict__ wire, int64_t rows, int cols, int row_bytes, int hdr, uint32_t l1,
+                        uint32_t l2, int R, float* __restrict__ out, int64_t ld, int32_t* __restrict__ status) {
+  extern __shared__ __align__(16) uint32_t sm_words[];
+  const int64_t nchunks = (rows + R - 1) / R;
+  int bad = 0;
+  for (int64_t ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    const int64_t r0 = ch * R;
+    const int nr = (int)min((int64_t)R, rows - r0);
+    const int nbytes = nr * row_bytes;
+    const uint8_t* src = wire + r0 * (int64_t)row_bytes;  // 16-byte aligned (R % 16 == 0, aligned base)
+    __syncthreads();
+    const int nvec = nbytes >> 4;
+    for (int v = threadIdx.x; v < nvec; v += blockDim.x)
+      reinterpret_cast<uint4*>(sm_words)[v] = __ldcs(reinterpret_cast<const uint4*>(src) + v);
+    for (int b = (nvec << 4) + threadIdx.x; b < nbytes; b += blockDim.x)
+      reinterpret_cast<uint8_t*>(sm_words)[b] = src[b];
+    if (threadIdx.x < 2) sm_words[(nbytes >> 2) + 1 + threadIdx.x] = 0;  // words touched by the last funnel shifts
+    __syncthreads();
+    const int total = nr * cols;
+    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+      const int r = idx / cols, c = idx - r * cols;
+      const int o = r * row_bytes + hdr + 11 * c;
+      const uint32_t tag = smem_u32_at(sm_words, o) & 0xffffffu;
+      const uint32_t lo = smem_u32_at(sm_words, o + 3), hi = smem_u32_at(sm_words, o + 7);
+      if (tag != 0x11090au) bad = 1;
+      out[(r0 + r) * ld + c] = (float)__hiloint2double((int)hi, (int)lo);
+      if (c == 0) {  // row header: 0a <varint L1> 32 <varint L2>
+        const uint8_t* h = reinterpret_cast<const uint8_t*>(sm_words) + r * row_bytes;
+        int pos = 0;
+        if (h[pos++] != 0x0a) bad = 1;
+        uint32_t v = 0; int shf = 0;
+        while (pos < hdr) { const uint8_t b = h[pos++]; v |= (uint32_t)(b & 0x7f) << shf; shf += 7; if (!(b & 0x80)) break; }
+        if (v != l1) bad = 1;
+        if (pos < hdr && h[pos++] != 0x32) bad = 1;
+        v = 0; shf = 0;
+        while (pos < hdr) { const uint8_t b = h[pos++]; v |= (uint32_t)(b & 0x7f) << shf; shf += 7; if (!(b & 0x80)) break; }
+        if (v != l2 || pos != hdr) bad = 1;
+      }
+    }
+  }
+  if (bad) atomicExch(status, 1);
+}
+
+template <typename TIn>
+__global__ void __launch_bounds__(256)
+pack_listvalue_staged(const TIn* __restrict__ in, int64_t rows, int cols, int row_bytes, int hdr, uint32_t l1,
+                      uint32_t l2, int R, uint8_t* __restrict__ out) {
+  extern __shared__ __align__(16) uint32_t sm_words[];
+  const int ncol = cols > 0 ? cols : 1;
+  const int64_t nchunks = (rows + R - 1) / R;
+  for (int64_t ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    const int64_t r0 = ch * R;
+    const int nr = (int)min((int64_t)R, rows - r0);
+    const int nbytes = nr * row_bytes;
+    __syncthreads();
+    for (int v = threadIdx.x; v < ((nbytes + 15) >> 4) + 1; v += blockDim.x)
+      reinterpret_cast<uint4*>(sm_words)[v] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();
+    const int total = nr * ncol;
+    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+      const int r = idx / ncol, c = idx - r * ncol;
+      const int o = r * row_bytes + hdr + 11 * c;
+      const double dv = (double)in[(r0 + r) * (int64_t)ncol + c];
+      const uint32_t lo = (uint32_t)__double2loint(dv), hi = (uint32_t)__double2hiint(dv);
+      // record bytes 0a 09 11 v0..v7 as three little-endian words, shifted to the byte offset inside the word
+      const uint32_t w0 = 0x0011090au | (lo << 24), w1 = (lo >> 8) | (hi << 24), w2 = hi >> 8;
+      const int k = o >> 2, sh = (o & 3) * 8;
+      atomicOr(sm_words + k, w0 << sh);
+      atomicOr(sm_words + k + 1, __funnelshift_l(w0, w1, sh));
+      atomicOr(sm_words + k + 2, __funnelshift_l(w1, w2, sh));
+      if (sh >= 16) atomicOr(sm_words + k + 3, __funnelshift_l(w2, 0u, sh));
+      if (cols > 0 && c == 0) {
+        uint8_t hb[12];
+        int pos = 0;
+        hb[pos++] = 0x0a;
+        uint32_t v = l1;
+        while (v >= 0x80) { hb[pos++] = (uint8_t)(v | 0x80); v >>= 7; }
+        hb[pos++] = (uint8_t)v;
+        hb[pos++] = 0x32;
+        v = l2;
+        while (v >= 0x80) { hb[pos++] = (uint8_t)(v | 0x80); v >>= 7; }
+        hb[pos++] = (uint8_t)v;
+        const int ob = r * row_bytes;
+        for (int b = 0; b < pos; ++b) atomicOr(sm_words + ((ob + b) >> 2), (uint32_t)hb[b] << (((ob + b) & 3) * 8));
+      }
+    }
+    __syncthreads();
+    uint8_t* dst = out + r0 * (int64_t)row_bytes;
+    const int nvec = nbytes >> 4;
+    for (int v = threadIdx.x; v < nvec; v += blockDim.x)
+      __stcs(reinterpret_cast<uint4*>(dst) + v, reinterpret_cast<const uint4*>(sm_words)[v]);
+    for (int b = (nvec << 4) + threadIdx.x; b < nbytes; b += blockDim.x) dst[b] = reinterpret_cast<const uint8_t*>(sm_words)[b];
+  }
+}
+
+// ---- cols % 4 == 0: four consecutive records (44 bytes = 11 words) per thread, no division, no per-byte work ----
+__global__ void __launch_bounds__(256)
+unpack_listvalue_staged4(const uint8_t* __restrict__ wire, int64_t rows, int cols, int row_bytes, int hdr, uint32_t l1,
+                         uint32_t l2, int R, float* __restrict__ out, int64_t ld, int32_t* __restrict__ status) {
+  extern __shared__ __align__(16) uint32_t sm_words[];
+  const int64_t nchunks = (rows + R - 1) / R;
+  const int q = cols >> 2;  // 4-record runs per row
+  const bool vec_out = (ld & 3) == 0 && (((uintptr_t)out) & 15) == 0;
+  int bad = 0;
+  for (int64_t ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    const int64_t r0 = ch * R;
+    const int nr = (int)min((int64_t)R, rows - r0);
+    const int nbytes = nr * row_bytes;
+    const uint8_t* src = wire + r0 * (int64_t)row_bytes;
+    __syncthreads();
+    const int nvec = nbytes >> 4;
+    for (int v = threadIdx.x; v < nvec; v += blockDim.x)
+      reinterpret_cast<uint4*>(sm_words)[v] = __ldcs(reinterpret_cast<const uint4*>(src) + v);
+    for (int b = (nvec << 4) + threadIdx.x; b < nbytes; b += blockDim.x)
+      reinterpret_cast<uint8_t*>(sm_words)[b] = src[b];
+    __syncthreads();
+    // (row, run) pairs: consecutive threads take consecutive runs of a row
+    const int total = nr * q;
+    int r = threadIdx.x / q, u = threadIdx.x - r * q;
+    const int dr = blockDim.x / q, du = blockDim.x - dr * q;
+    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+      const int o = r * row_bytes + hdr + 44 * u;  // byte offset of the first of 4 records
+      const int k = o >> 2, sh = (o & 3) * 8;
+      uint32_t w[12];
+#pragma unroll
+      for (int i = 0; i < 12; ++i) w[i] = sm_words[k + i];
+      uint32_t a[11];  // the 44 bytes, word aligned
+#pragma unroll
+      for (int i = 0; i < 11; ++i) a[i] = __funnelshift_r(w[i], w[i + 1], sh);
+      float v[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        // record e occupies bytes 11e .. 11e+10 of a[]: tag at 11e, value at 11e+3
+        const int tb = 11 * e, vb = tb + 3;
+        const uint32_t tag = __funnelshift_r(a[tb >> 2], a[(tb >> 2) + 1 < 11 ? (tb >> 2) + 1 : 10], (tb & 3) * 8) & 0xffffffu;
+        const uint32_t lo = __funnelshift_r(a[vb >> 2], a[(vb >> 2) + 1], (vb & 3) * 8);
+        const uint32_t hi = (vb >> 2) + 2 < 11 ? __funnelshift_r(a[(vb >> 2) + 1], a[(vb >> 2) + 2], (vb & 3) * 8)
+                                               : (a[(vb >> 2) + 1] >> ((vb & 3) * 8));
+        if (tag != 0x11090au) bad = 1;
+        v[e] = (float)__hiloint2double((int)hi, (int)lo);
+      }
+      float* dst = out + (r0 + r) * ld + 4 * u;
+      if (vec_out) *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+      else { dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2]; dst[3] = v[3]; }
+      if (u == 0) {
+        const uint8_t* h = reinterpret_cast<const uint8_t*>(sm_words) + r * row_bytes;
+        int pos = 0;
+        if (h[pos++] != 0x0a) bad = 1;
+        uint32_t vv = 0; int shf = 0;
+        while (pos < hdr) { const uint8_t b = h[pos++]; vv |= (uint32_t)(b & 0x7f) << shf; shf += 7; if (!(b & 0x80)) break; }
+        if (vv != l1) bad = 1;
+        if (pos < hdr && h[pos++] != 0x32) bad = 1;
+        vv = 0; shf = 0;
+        while (pos < hdr) { const uint8_t b = h[pos++]; vv |= (uint32_t)(b & 0x7f) << shf; shf += 7; if (!(b & 0x80)) break; }
+        if (vv != l2 || pos != hdr) bad = 1;
+      }
+      r += dr; u += du;
+      if (u >= q) { u -= q; ++r; }
+    }
+  }
+  if (bad) atomicExch(status, 1);
+}
+
+template <typename TIn>
+__global__ void __launch_bounds__(256)
+pack_listvalue_staged4(const TIn* __restrict__ in, int64_t rows, int cols, int row_bytes, int hdr, uint32_t l1,
+                       uint32_t l2, int R, uint8_t* __restrict__ out) {
+  extern __shared__ __align__(16) uint32_t sm_words[];
+  const int64_t nchunks = (rows + R - 1) / R;
+  const int q = cols >> 2;
+  for (int64_t ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    const int64_t r0 = ch * R;
+    const int nr = (int)min((int64_t)R, rows - r0);
+    const int nbytes = nr * row_bytes;
+    __syncthreads();
+    // only the words shared between neighbours are OR-ed into, so only the header area / row edges need zeroing;
+    // zero everything (cheap) to keep it simple
+    for (int v = threadIdx.x; v < ((nbytes + 15) >> 4) + 1; v += blockDim.x)
+      reinterpret_cast<uint4*>(sm_words)[v] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();
+    const int total = nr * q;
+    int r = threadIdx.x / q, u = threadIdx.x - r * q;
+    const int dr = blockDim.x / q, du = blockDim.x - dr * q;
+    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+      const TIn* src = in + (r0 + r) * (int64_t)cols + 4 * u;
+      uint32_t a[12];  // 44 bytes of four records + one spill word
+      a[11] = 0;
+      uint32_t lo[4], hi[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const double dv = (double)src[e];
+        lo[e] = (uint32_t)__double2loint(dv);
+        hi[e] = (uint32_t)__double2hiint(dv);
+      }
+      // bytes: [0a 09 11 v0..v7] x 4, little endian words
+      a[0] = 0x0011090au | (lo[0] << 24);
+      a[1] = (lo[0] >> 8) | (hi[0] << 24);
+      a[2] = (hi[0] >> 8) | 0x0a000000u;
+      a[3] = 0x00001109u | (lo[1] << 16);
+      a[4] = (lo[1] >> 16) | (hi[1] << 16);
+      a[5] = (hi[1] >> 16) | 0x090a0000u;
+      a[6] = 0x00000011u | (lo[2] << 8);
+      a[7] = (lo[2] >> 24) | (hi[2] << 8);
+      a[8] = (hi[2] >> 24) | 0x11090a00u;
+      a[9] = lo[3];
+      a[10] = hi[3];
+      const int o = r * row_bytes + hdr + 44 * u;
+      const int k = o >> 2, sh = (o & 3) * 8;
+      if (sh == 0) {
+#pragma unroll
+        for (int i = 0; i < 11; ++i) sm_words[k + i] = a[i];
+      } else {
+        atomicOr(sm_words + k, a[0] << sh);  // first and last words are shared with the neighbouring runs / header
+#pragma unroll
+        for (int i = 1; i < 11; ++i) sm_words[k + i] = __funnelshift_l(a[i - 1], a[i], sh);
+        atomicOr(sm_words + k + 11, a[10] >> (32 - sh));
+      }
+      if (u == 0) {
+        uint8_t hb[12];
+        int pos = 0;
+        hb[pos++] = 0x0a;
+        uint32_t v = l1;
+        while (v >= 0x80) { hb[pos++] = (uint8_t)(v | 0x80); v >>= 7; }
+        hb[pos++] = (uint8_t)v;
+        hb[pos++] = 0x32;
+        v = l2;
+        while (v >= 0x80) { hb[pos++] = (uint8_t)(v | 0x80); v >>= 7; }
+        hb[pos++] = (uint8_t)v;
+        const int ob = r * row_bytes;
+        for (int b = 0; b < pos; ++b) atomicOr(sm_words + ((ob + b) >> 2), (uint32_t)hb[b] << (((ob + b) & 3) * 8));
+      }
+      r += dr; u += du;
+      if (u >= q) { u -= q; ++r; }
+    }
+    __syncthreads();
+    uint8_t* dst = out + r0 * (int64_t)row_bytes;
+    const int nvec = nbytes >> 4;
+    for (int v = threadIdx.x; v < nvec; v += blockDim.x)
+      __stcs(reinterpret_cast<uint4*>(dst) + v, reinterpret_cast<const uint4*>(sm_words)[v]);
+    for (int b = (nvec << 4) + threadIdx.x; b < nbytes; b += blockDim.x) dst[b] = reinterpret_cast<const uint8_t*>(sm_words)[b];
+  }
+}
+
+// rows per staged chunk: a multiple of 16 with the chunk near 32 KB; 0 = row too long for shared memory
+int staged_rows(int64_t row_bytes) {
+  if (row_bytes * 16 + 64 > 200 * 1024) return 0;
+  static const int64_t target = getenv("SB200_LV_CHUNK") ? atoll(getenv("SB200_LV_CHUNK")) : 32 * 1024;
+  int64_t m = target / (row_bytes * 16);
+  if (m < 1) m = 1;
+  return (int)(16 * m);
+}
+
 int grid_for(int64_t total, int per_thread) {
   int64_t want = sb::ceil_div(total, 256 * (int64_t)per_thread);
   if (want < 1) want = 1;
@@ -191,7 +455,23 @@ extern "C" int32_t sb_unpack_listvalue(const uint8_t* d_wire, uint64_t nbytes, i
   SB_REQUIRE(d_wire && d_out, SB_ERR_INVALID, "sb_unpack_listvalue: null buffer");
   int64_t rb; int hdr; uint64_t l1, l2;
   listvalue_layout(cols, &rb, &hdr, &l1, &l2);
-  unpack_listvalue_kernel<<<grid_for(rows * cols, 4), 256, 0, st>>>(d_wire, rows, cols, rb, hdr, l1, l2, d_out, ld, d_status);
+  const int R = staged_rows(rb);
+  if (R > 0 && ((uintptr_t)d_wire & 15) == 0 && cols < (1 << 20)) {
+    const size_t smem = (size_t)R * rb + 64;
+    SB_CUDA(cudaFuncSetAttribute(unpack_listvalue_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    int64_t nch = sb::ceil_div(rows, R);
+    int grid = (int)(nch < (int64_t)sb::kNumSMs * 12 ? nch : (int64_t)sb::kNumSMs * 12);
+    if (cols % 4 == 0) {
+      SB_CUDA(cudaFuncSetAttribute(unpack_listvalue_staged4, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      unpack_listvalue_staged4<<<grid, 256, smem, st>>>(d_wire, rows, (int)cols, (int)rb, hdr, (uint32_t)l1, (uint32_t)l2,
+                                                       R, d_out, ld, d_status);
+    } else {
+      unpack_listvalue_staged<<<grid, 256, smem, st>>>(d_wire, rows, (int)cols, (int)rb, hdr, (uint32_t)l1, (uint32_t)l2,
+                                                      R, d_out, ld, d_status);
+    }
+  } else {
+    unpack_listvalue_kernel<<<grid_for(rows * cols, 4), 256, 0, st>>>(d_wire, rows, cols, rb, hdr, l1, l2, d_out, ld, d_status);
+  }
   SB_LAUNCH_CHECK();
   return SB_OK;
 }
@@ -221,10 +501,33 @@ extern "C" int32_t sb_pack_listvalue(const void* d_in, int32_t in_dtype, int64_t
   if (cols > 0) listvalue_layout(cols, &rb, &hdr, &l1, &l2);
   cudaStream_t st = (cudaStream_t)stream;
   const int grid = grid_for(rows * (cols > 0 ? cols : 1), 4);
-  if (in_dtype == SB_F32)
+  const int R = staged_rows(rb);
+  if (R > 0 && ((uintptr_t)d_wire & 15) == 0 && cols < (1 << 20)) {
+    const size_t smem = (size_t)R * rb + 64;
+    int64_t nch = sb::ceil_div(rows, R);
+    int g2 = (int)(nch < (int64_t)sb::kNumSMs * 12 ? nch : (int64_t)sb::kNumSMs * 12);
+    if (cols > 0 && cols % 4 == 0 && in_dtype == SB_F32) {
+      SB_CUDA(cudaFuncSetAttribute(pack_listvalue_staged4<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      pack_listvalue_staged4<float><<<g2, 256, smem, st>>>((const float*)d_in, rows, (int)cols, (int)rb, hdr, (uint32_t)l1,
+                                                          (uint32_t)l2, R, d_wire);
+    } else if (cols > 0 && cols % 4 == 0) {
+      SB_CUDA(cudaFuncSetAttribute(pack_listvalue_staged4<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      pack_listvalue_staged4<int32_t><<<g2, 256, smem, st>>>((const int32_t*)d_in, rows, (int)cols, (int)rb, hdr,
+                                                            (uint32_t)l1, (uint32_t)l2, R, d_wire);
+    } else if (in_dtype == SB_F32) {
+      SB_CUDA(cudaFuncSetAttribute(pack_listvalue_staged<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      pack_listvalue_staged<float><<<g2, 256, smem, st>>>((const float*)d_in, rows, (int)cols, (int)rb, hdr, (uint32_t)l1,
+                                                         (uint32_t)l2, R, d_wire);
+    } else {
+      SB_CUDA(cudaFuncSetAttribute(pack_listvalue_staged<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      pack_listvalue_staged<int32_t><<<g2, 256, smem, st>>>((const int32_t*)d_in, rows, (int)cols, (int)rb, hdr,
+                                                           (uint32_t)l1, (uint32_t)l2, R, d_wire);
+    }
+  } else if (in_dtype == SB_F32) {
     pack_listvalue_kernel<float><<<grid, 256, 0, st>>>((const float*)d_in, rows, cols, rb, hdr, l1, l2, d_wire);
-  else
+  } else {
     pack_listvalue_kernel<int32_t><<<grid, 256, 0, st>>>((const int32_t*)d_in, rows, cols, rb, hdr, l1, l2, d_wire);
+  }
   SB_LAUNCH_CHECK();
   return SB_OK;
 }
