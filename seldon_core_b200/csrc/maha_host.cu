@@ -32,7 +32,7 @@ uint64_t carve(const sb_maha* h, int64_t nsub_max, int64_t rows_max, void* base,
   uint64_t o_rp = take(KQ * sizeof(double));
   uint64_t o_sl = take((uint64_t)reduce_slices((int)d) * PS * sizeof(double));
   uint64_t o_ct = take((uint64_t)(nsub_max / 32 + 2) * KQ * sizeof(double));
-  const bool split = h->d == 64 && h->KP == 16;
+  const bool split = (h->d == 64 || h->d == 128 || h->d == 256) && h->KP == 16;
   uint64_t o_pz = take(split ? (uint64_t)rows_max * 16 * sizeof(float) : 0);
   uint64_t o_pd = take(split ? (uint64_t)rows_max * 16 * sizeof(float) : 0);
   uint64_t o_pf = take(split ? (uint64_t)rows_max : 0);

@@ -882,20 +882,36 @@ score_chain64(const float* __restrict__ X, int64_t ld, SubLayout lay, const floa
 // Cost: ~150 B/row of extra DRAM traffic on top of the algorithmic 4*d + 8.
 constexpr int kProjEvCap = 512;   // clipped elements listed per 16-row block; denser blocks take the slow path
 
-template <bool CLIP>
-__global__ void __launch_bounds__(128, 4)
-project64(const float* __restrict__ X, int64_t ld, int64_t rows, const float* __restrict__ mean_f,
-          const float* __restrict__ lo_f, const float* __restrict__ hi_f, const float* __restrict__ Vf,
-          float* __restrict__ Zout, float* __restrict__ Dout, uint8_t* __restrict__ cflag) {
-  constexpr int KP = 16, D = 64;
-  __shared__ __align__(16) float ms[D], los[D], his[D];
-  __shared__ __align__(16) float Vs[CLIP ? D * KP : 4];
-  __shared__ __align__(16) uint4 vfrag[16 * 32];
-  __shared__ __align__(16) float2 evlist[4][CLIP ? kProjEvCap : 1];
-  __shared__ __align__(16) float dtile[4][CLIP ? 16 * KP : 4];
-  __shared__ int evcnt[4];
+// shared-memory carve-up of project_rows<NB>: sizes in bytes
+__host__ __device__ constexpr size_t proj_smem_bytes(int NB, bool clip) {
+  return (size_t)3 * 64 * NB * 4                      // mean, lo, hi
+         + (clip ? (size_t)64 * NB * 16 * 4 : 16)     // fp32 eigenvectors (sparse clip correction)
+         + (size_t)NB * 16 * 32 * 16                  // B fragments
+         + (clip ? (size_t)4 * kProjEvCap * 8 : 16)   // event lists, one per warp
+         + (clip ? (size_t)4 * 16 * 16 * 4 : 16)      // y - z tiles, one per warp
+         + 64;                                        // event counters
+}
+
+// d = 64*NB, k <= 16.  Each warp projects blocks of 16 rows: 3xTF32 mma.sync over NB column chunks of 64 features.
+template <int NB, bool CLIP>
+__global__ void __launch_bounds__(128, NB == 1 ? 4 : 3)
+project_rows(const float* __restrict__ X, int64_t ld, int64_t rows, const float* __restrict__ mean_f,
+             const float* __restrict__ lo_f, const float* __restrict__ hi_f, const float* __restrict__ Vf,
+             float* __restrict__ Zout, float* __restrict__ Dout, uint8_t* __restrict__ cflag) {
+  constexpr int KP = 16, D = 64 * NB;
+  extern __shared__ __align__(16) unsigned char proj_smem[];
+  float* ms = reinterpret_cast<float*>(proj_smem);
+  float* los = ms + D;
+  float* his = los + D;
+  float* Vs = his + D;
+  uint4* vfrag = reinterpret_cast<uint4*>(Vs + (CLIP ? D * KP : 4));
+  float2* evbase = reinterpret_cast<float2*>(vfrag + NB * 16 * 32);
+  float* dtbase = reinterpret_cast<float*>(evbase + (CLIP ? 4 * kProjEvCap : 2));
+  int* evcnt = reinterpret_cast<int*>(dtbase + (CLIP ? 4 * 16 * KP : 4));
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
+  float2* evlist = evbase + (CLIP ? warp * kProjEvCap : 0);
+  float* dt = dtbase + (CLIP ? warp * 16 * KP : 0);
   for (int f = threadIdx.x; f < D; f += blockDim.x) {
     ms[f] = mean_f[f];
     los[f] = CLIP ? lo_f[f] : 0.f;
@@ -903,9 +919,9 @@ project64(const float* __restrict__ X, int64_t ld, int64_t rows, const float* __
   }
   if (CLIP)
     for (int idx = threadIdx.x; idx < D * KP; idx += blockDim.x) Vs[idx] = Vf[idx];
-  for (int idx = threadIdx.x; idx < 16 * 32; idx += blockDim.x) {
-    const int fr = idx >> 5, ln = idx & 31, ks = fr >> 1, nt = fr & 1, gg = ln >> 2, tt = ln & 3;
-    const int f0 = 16 * (ks >> 1) + 4 * tt + 2 * (ks & 1);
+  for (int idx = threadIdx.x; idx < NB * 16 * 32; idx += blockDim.x) {
+    const int fr = idx >> 5, ln = idx & 31, cc = fr >> 4, ks = (fr >> 1) & 7, nt = fr & 1, gg = ln >> 2, tt = ln & 3;
+    const int f0 = 64 * cc + 16 * (ks >> 1) + 4 * tt + 2 * (ks & 1);
     const float v0 = Vf[f0 * KP + 8 * nt + gg], v1 = Vf[(f0 + 1) * KP + 8 * nt + gg];
     uint4 fr4;
     fr4.x = to_tf32(v0);
@@ -921,19 +937,19 @@ project64(const float* __restrict__ X, int64_t ld, int64_t rows, const float* __
   const int64_t wstride = (int64_t)gridDim.x * 4;
   int64_t blk = (int64_t)blockIdx.x * 4 + warp;
   float4 xa[4], xb[4];
-  auto load_rows = [&](int64_t b) {
+  auto load_rows = [&](int64_t b, int cc) {
     const int64_t rb = b << 4;
     const bool va = b < nblocks && rb + g < rows, vb8 = b < nblocks && rb + g + 8 < rows;
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    const float4* pa = reinterpret_cast<const float4*>(X + (rb + g) * ld);
-    const float4* pb = reinterpret_cast<const float4*>(X + (rb + g + 8) * ld);
+    const float4* pa = reinterpret_cast<const float4*>(X + (rb + g) * ld + 64 * cc);
+    const float4* pb = reinterpret_cast<const float4*>(X + (rb + g + 8) * ld + 64 * cc);
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       xa[q] = va ? ldg_stream_f4(pa + 4 * q + t) : zero4;
       xb[q] = vb8 ? ldg_stream_f4(pb + 4 * q + t) : zero4;
     }
   };
-  load_rows(blk);
+  load_rows(blk, 0);
   for (; blk < nblocks; blk += wstride) {
     const int64_t rb = blk << 4;
     const bool va = rb + g < rows, vb8 = rb + g + 8 < rows;
@@ -942,64 +958,73 @@ project64(const float* __restrict__ X, int64_t ld, int64_t rows, const float* __
     for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
       for (int e = 0; e < 4; ++e) accz[nt][e] = 0.f;
+#pragma unroll 1
+    for (int cc = 0; cc < NB; ++cc) {
+      float ra[4][4], rbv[4][4];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const float4 m4 = *reinterpret_cast<const float4*>(ms + 16 * q + 4 * t);
-      const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
-      float ra[4] = {xa[q].x, xa[q].y, xa[q].z, xa[q].w};
-      float rbv[4] = {xb[q].x, xb[q].y, xb[q].z, xb[q].w};
-      if (CLIP) {
-        const float4 l4 = *reinterpret_cast<const float4*>(los + 16 * q + 4 * t);
-        const float4 h4 = *reinterpret_cast<const float4*>(his + 16 * q + 4 * t);
-        const float ll[4] = {l4.x, l4.y, l4.z, l4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w};
-        float ca[4], cb[4];
-        bool anyc = false;
+      for (int q = 0; q < 4; ++q) {
+        ra[q][0] = xa[q].x; ra[q][1] = xa[q].y; ra[q][2] = xa[q].z; ra[q][3] = xa[q].w;
+        rbv[q][0] = xb[q].x; rbv[q][1] = xb[q].y; rbv[q][2] = xb[q].z; rbv[q][3] = xb[q].w;
+      }
+      // next chunk (or the first chunk of the warp's next block) in flight while this one is multiplied
+      if (cc + 1 < NB) load_rows(blk, cc + 1); else load_rows(blk + wstride, 0);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          ca[e] = fminf(fmaxf(ra[e], ll[e]), hh[e]);
-          cb[e] = fminf(fmaxf(rbv[e], ll[e]), hh[e]);
-          anyc = anyc || (ca[e] != ra[e]) || (cb[e] != rbv[e]);
-        }
-        if (anyc) {  // rare: list the clipped elements of this lane
+      for (int q = 0; q < 4; ++q) {
+        const int cbase = 64 * cc + 16 * q + 4 * t;
+        const float4 m4 = *reinterpret_cast<const float4*>(ms + cbase);
+        const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
+        if (CLIP) {
+          const float4 l4 = *reinterpret_cast<const float4*>(los + cbase);
+          const float4 h4 = *reinterpret_cast<const float4*>(his + cbase);
+          const float ll[4] = {l4.x, l4.y, l4.z, l4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w};
+          float ca[4], cb[4];
+          bool anyc = false;
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
+            ca[e] = fminf(fmaxf(ra[q][e], ll[e]), hh[e]);
+            cb[e] = fminf(fmaxf(rbv[q][e], ll[e]), hh[e]);
+            anyc = anyc || (ca[e] != ra[q][e]) || (cb[e] != rbv[q][e]);
+          }
+          if (anyc) {  // rare: list the clipped elements of this lane
 #pragma unroll
-            for (int rr = 0; rr < 2; ++rr) {
-              const float x = rr == 0 ? ra[e] : rbv[e];
-              const float xc = rr == 0 ? ca[e] : cb[e];
-              if (xc != x && (rr == 0 ? va : vb8)) {
-                const int slot = atomicAdd(&evcnt[warp], 1);
-                if (slot < kProjEvCap)
-                  evlist[warp][slot] = make_float2(__int_as_float((rr == 0 ? g : g + 8) * 64 + 16 * q + 4 * t + e), x - xc);
+            for (int e = 0; e < 4; ++e) {
+#pragma unroll
+              for (int rr = 0; rr < 2; ++rr) {
+                const float x = rr == 0 ? ra[q][e] : rbv[q][e];
+                const float xc = rr == 0 ? ca[e] : cb[e];
+                if (xc != x && (rr == 0 ? va : vb8)) {
+                  const int slot = atomicAdd(&evcnt[warp], 1);
+                  if (slot < kProjEvCap)
+                    evlist[slot] = make_float2(__int_as_float((rr == 0 ? g : g + 8) * D + cbase + e), x - xc);
+                }
               }
             }
           }
+#pragma unroll
+          for (int e = 0; e < 4; ++e) { ra[q][e] = ca[e]; rbv[q][e] = cb[e]; }
+        }
+        uint32_t zb[2][4], zs[2][4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float da = ra[q][e] - mm[e], db = rbv[q][e] - mm[e];
+          zb[0][e] = to_tf32(da);
+          zs[0][e] = to_tf32(da - __uint_as_float(zb[0][e]));
+          zb[1][e] = to_tf32(db);
+          zs[1][e] = to_tf32(db - __uint_as_float(zb[1][e]));
         }
 #pragma unroll
-        for (int e = 0; e < 4; ++e) { ra[e] = ca[e]; rbv[e] = cb[e]; }
-      }
-      uint32_t zb[2][4], zs[2][4];
+        for (int half = 0; half < 2; ++half) {
+          const int ks = 2 * q + half, e0 = 2 * half;
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float da = ra[e] - mm[e], db = rbv[e] - mm[e];
-        zb[0][e] = to_tf32(da);
-        zs[0][e] = to_tf32(da - __uint_as_float(zb[0][e]));
-        zb[1][e] = to_tf32(db);
-        zs[1][e] = to_tf32(db - __uint_as_float(zb[1][e]));
-      }
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        const int ks = 2 * q + half, e0 = 2 * half;
-#pragma unroll
-        for (int nt = 0; nt < 2; ++nt) {
-          const uint4 vf = vfrag[(ks * 2 + nt) * 32 + lane];
-          mma_m16n8k8_tf32(accz[nt], zs[0][e0], zs[1][e0], zs[0][e0 + 1], zs[1][e0 + 1], vf.x, vf.y);
-          mma_m16n8k8_tf32(accz[nt], zb[0][e0], zb[1][e0], zb[0][e0 + 1], zb[1][e0 + 1], vf.z, vf.w);
-          mma_m16n8k8_tf32(accz[nt], zb[0][e0], zb[1][e0], zb[0][e0 + 1], zb[1][e0 + 1], vf.x, vf.y);
+          for (int nt = 0; nt < 2; ++nt) {
+            const uint4 vf = vfrag[((cc * 8 + ks) * 2 + nt) * 32 + lane];
+            mma_m16n8k8_tf32(accz[nt], zs[0][e0], zs[1][e0], zs[0][e0 + 1], zs[1][e0 + 1], vf.x, vf.y);
+            mma_m16n8k8_tf32(accz[nt], zb[0][e0], zb[1][e0], zb[0][e0 + 1], zb[1][e0 + 1], vf.z, vf.w);
+            mma_m16n8k8_tf32(accz[nt], zb[0][e0], zb[1][e0], zb[0][e0 + 1], zb[1][e0 + 1], vf.x, vf.y);
+          }
         }
       }
     }
-    load_rows(blk + wstride);  // next block in flight while this one is written out
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
       const int c0 = 8 * nt + 2 * t;
@@ -1011,7 +1036,6 @@ project64(const float* __restrict__ X, int64_t ld, int64_t rows, const float* __
       __syncwarp();
       const int nev = evcnt[warp];  // warp-uniform
       if (nev > 0) {
-        float* dt = dtile[warp];
 #pragma unroll
         for (int i = 0; i < 2; ++i) reinterpret_cast<float4*>(dt)[lane + 32 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
         __syncwarp();
@@ -1019,8 +1043,8 @@ project64(const float* __restrict__ X, int64_t ld, int64_t rows, const float* __
         const int half = lane >> 4, jj = lane & 15;
         if (nev <= kProjEvCap) {
           for (int k = 0; k < nev; ++k) {
-            const float2 ev = evlist[warp][k];
-            const int rc = __float_as_int(ev.x), row = rc >> 6, col = rc & 63;
+            const float2 ev = evlist[k];
+            const int rc = __float_as_int(ev.x), row = rc / D, col = rc - row * D;
             rowmask |= 1u << row;
             if ((k & 1) == half) atomicAdd(dt + row * KP + jj, ev.y * Vs[col * KP + jj]);
           }
@@ -1299,31 +1323,41 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
                                    flag);
     SB_LAUNCH_CHECK();
   }
-  const bool fast = KP == 16 && d == 64 && !h->force_generic && (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
+  const bool aligned = (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
+  const bool fast = KP == 16 && d == 64 && !h->force_generic && aligned;
+  const bool split = KP == 16 && (d == 64 || d == 128 || d == 256) && !h->force_generic && aligned && !h->fused_pass2;
   if (h->profile) { cudaEventRecord(h->ev[6], st); cudaEventRecord(h->ev[7], st); cudaEventRecord(h->ev[8], st); }
-  if (fast && !h->fused_pass2) {
+  if (split) {
     const int64_t nblocks = ceil_div(h->rows_local, 16);
+    const int NBv = d / 64;
     int pgrid = (int)ceil_div(nblocks, 4);
-    if (pgrid > kNumSMs * 4) pgrid = kNumSMs * 4;
+    const int pmax = kNumSMs * (NBv == 1 ? 4 : 3);
+    if (pgrid > pmax) pgrid = pmax;
     int cgrid = (int)ceil_div(nsub, 16);
     if (cgrid > kNumSMs * 2) cgrid = kNumSMs * 2;
+#define SB_LAUNCH_PROJECT(NB, CLIPV)                                                                               \
+    do {                                                                                                           \
+      const size_t psm = proj_smem_bytes(NB, CLIPV);                                                               \
+      SB_CUDA(cudaFuncSetAttribute(project_rows<NB, CLIPV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psm)); \
+      project_rows<NB, CLIPV><<<pgrid, 128, psm, st>>>(X, ld, h->rows_local, h->d_mean_f, h->d_lo_f, h->d_hi_f,    \
+                                                      h->d_Vf, ws.proj_Z, ws.proj_D, ws.proj_flag);                \
+    } while (0)
     if (h->use_clip) {
-      project64<true><<<pgrid, 128, 0, st>>>(X, ld, h->rows_local, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf,
-                                            ws.proj_Z, ws.proj_D, ws.proj_flag);
+      if (NBv == 1) SB_LAUNCH_PROJECT(1, true); else if (NBv == 2) SB_LAUNCH_PROJECT(2, true); else SB_LAUNCH_PROJECT(4, true);
       SB_LAUNCH_CHECK();
       if (h->profile) { cudaEventRecord(h->ev[7], st); cudaEventRecord(h->ev[8], st); }
       chain16<true><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
                                           (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
                                           h->d_score_sum, score, flag);
     } else {
-      project64<false><<<pgrid, 128, 0, st>>>(X, ld, h->rows_local, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf,
-                                             ws.proj_Z, ws.proj_D, ws.proj_flag);
+      if (NBv == 1) SB_LAUNCH_PROJECT(1, false); else if (NBv == 2) SB_LAUNCH_PROJECT(2, false); else SB_LAUNCH_PROJECT(4, false);
       SB_LAUNCH_CHECK();
       if (h->profile) { cudaEventRecord(h->ev[7], st); cudaEventRecord(h->ev[8], st); }
       chain16<false><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
                                            (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
                                            h->d_score_sum, score, flag);
     }
+#undef SB_LAUNCH_PROJECT
   } else if (fast) {
     int grid = (int)ceil_div(nsub, 8);
     if (grid > kNumSMs * 3) grid = kNumSMs * 3;

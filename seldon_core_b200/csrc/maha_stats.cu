@@ -187,6 +187,202 @@ pass1_gram64_tf32(const float* __restrict__ X, int64_t ld, SubLayout lay, const 
   }
 }
 
+// ---------------------------------------------------------------------- d = 128 / 256, tensor cores, blocked
+// The D x D Gram is cut into 64 x 64 blocks; only blocks on or above the diagonal are computed.  A warp owns one
+// "unit": a diagonal block (20 of its 32 mma tiles, as in pass1_gram64_tf32) or half of an off-diagonal block
+// (2 x 8 tiles).  NB*NB units per sub-segment (NB = D/64), 8 units per 256-thread CTA, so D = 256 uses two CTAs per
+// sub-segment; all warps of a sub-segment stream the same rows, the repeats hit L1/L2.  At these widths the kernel
+// is bound by the (legacy mma.sync) tensor pipe, not by HBM: 2*D*D*(NB+1)/(2*NB) flop per row per TF32 term.
+template <int NB, bool CLIP, int TERMS>
+__global__ void __launch_bounds__(NB == 2 ? 128 : 256, 1)
+pass1_gram_blocked_tf32(const float* __restrict__ X, int64_t ld, SubLayout lay, const float* __restrict__ mean_f,
+                        const float* __restrict__ lo_f, const float* __restrict__ hi_f, float* __restrict__ partials) {
+  constexpr int D = 64 * NB, PS = D + D * D;
+  constexpr int UNITS = NB * NB, CTAS_PER_SUB = (UNITS + 7) / 8;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int unit = (blockIdx.x % CTAS_PER_SUB) * 8 + warp;
+  if (unit >= UNITS) return;
+  // decode the unit
+  int bi, bj, hh = 0;
+  const bool diag = unit < NB;
+  if (diag) { bi = bj = unit; }
+  else {
+    int o = unit - NB;
+    hh = o & 1;
+    int p = o >> 1;  // p-th pair (bi < bj) in row-major order
+    bi = 0;
+    while (p >= NB - 1 - bi) { p -= NB - 1 - bi; ++bi; }
+    bj = bi + 1 + p;
+  }
+  const int ca = 64 * bi, cb = 64 * bj;
+  const int subs_stride = gridDim.x / CTAS_PER_SUB;
+
+  for (int sub = blockIdx.x / CTAS_PER_SUB; sub < lay.nsub; sub += subs_stride) {
+    const int64_t r0 = sub_begin(lay, sub), r1 = sub_begin(lay, sub + 1);
+    float* part = partials + (size_t)sub * PS;
+    float* G = part + D;
+    if (diag) {
+      // ---- diagonal block: identical to the d = 64 kernel on columns ca .. ca+63
+      float m[8], lo[8], hi[8];
+#pragma unroll
+      for (int jj = 0; jj < 8; ++jj) {
+        const int col = ca + (jj < 4 ? 4 * g + jj : 32 + 4 * g + (jj - 4));
+        m[jj] = mean_f[col];
+        if (CLIP) { lo[jj] = lo_f[col]; hi[jj] = hi_f[col]; }
+      }
+      float acc[4][8][4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[i][j][e] = 0.f;
+      float ssum[8];
+#pragma unroll
+      for (int jj = 0; jj < 8; ++jj) ssum[jj] = 0.f;
+      for (int64_t r = r0; r < r1; r += 8) {
+        const int64_t ra = r + t, rb = r + t + 4;
+        const bool va = ra < r1, vb = rb < r1;
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4* pa = reinterpret_cast<const float4*>(X + ra * ld + ca);
+        const float4* pb = reinterpret_cast<const float4*>(X + rb * ld + ca);
+        const float4 v0 = va ? __ldg(pa + g) : z4, v1 = va ? __ldg(pa + 8 + g) : z4;
+        const float4 v2 = vb ? __ldg(pb + g) : z4, v3 = vb ? __ldg(pb + 8 + g) : z4;
+        const float x[2][8] = {{v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w},
+                               {v2.x, v2.y, v2.z, v2.w, v3.x, v3.y, v3.z, v3.w}};
+        uint32_t big[2][8], sml[2][8];
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+          const bool valid = rr == 0 ? va : vb;
+#pragma unroll
+          for (int jj = 0; jj < 8; ++jj) {
+            float v = x[rr][jj];
+            if (CLIP) v = fminf(fmaxf(v, lo[jj]), hi[jj]);
+            v = valid ? v - m[jj] : 0.f;
+            ssum[jj] += v;
+            big[rr][jj] = to_tf32(v);
+            if (TERMS == 3) sml[rr][jj] = to_tf32(v - __uint_as_float(big[rr][jj]));
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (j >= 2 * i) {
+              if (TERMS == 3) {
+                mma_m16n8k8_tf32(acc[i][j], sml[0][2 * i], sml[0][2 * i + 1], sml[1][2 * i], sml[1][2 * i + 1], big[0][j], big[1][j]);
+                mma_m16n8k8_tf32(acc[i][j], big[0][2 * i], big[0][2 * i + 1], big[1][2 * i], big[1][2 * i + 1], sml[0][j], sml[1][j]);
+              }
+              mma_m16n8k8_tf32(acc[i][j], big[0][2 * i], big[0][2 * i + 1], big[1][2 * i], big[1][2 * i + 1], big[0][j], big[1][j]);
+            }
+      }
+#pragma unroll
+      for (int jj = 0; jj < 8; ++jj) {
+        float v = ssum[jj];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        if (t == 0) part[ca + (jj < 4 ? 4 * g + jj : 32 + 4 * g + (jj - 4))] = v;
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (j >= 2 * i) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int Lm = 16 * i + g + ((e & 2) ? 8 : 0), Ln = 8 * j + 2 * t + (e & 1);
+              if (Lm <= Ln) {
+                const int pm = ca + phys64(Lm), pn = ca + phys64(Ln);
+                G[(size_t)pm * D + pn] = acc[i][j][e];
+                G[(size_t)pn * D + pm] = acc[i][j][e];
+              }
+            }
+          }
+    } else {
+      // ---- half of an off-diagonal block: m-tiles {2hh, 2hh+1} of block bi against all 8 n-tiles of block bj
+      float ma[4], loa[4], hia[4], mb[8], lob[8], hib[8];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int col = ca + 32 * hh + 4 * g + q;
+        ma[q] = mean_f[col];
+        if (CLIP) { loa[q] = lo_f[col]; hia[q] = hi_f[col]; }
+      }
+#pragma unroll
+      for (int jj = 0; jj < 8; ++jj) {
+        const int col = cb + (jj < 4 ? 4 * g + jj : 32 + 4 * g + (jj - 4));
+        mb[jj] = mean_f[col];
+        if (CLIP) { lob[jj] = lo_f[col]; hib[jj] = hi_f[col]; }
+      }
+      float acc[2][8][4];
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[i][j][e] = 0.f;
+      for (int64_t r = r0; r < r1; r += 8) {
+        const int64_t ra = r + t, rb = r + t + 4;
+        const bool va = ra < r1, vb = rb < r1;
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float* rowa = X + ra * ld;
+        const float* rowb = X + rb * ld;
+        const float4 a0 = va ? __ldg(reinterpret_cast<const float4*>(rowa + ca + 32 * hh) + g) : z4;
+        const float4 a1 = vb ? __ldg(reinterpret_cast<const float4*>(rowb + ca + 32 * hh) + g) : z4;
+        const float4 b0 = va ? __ldg(reinterpret_cast<const float4*>(rowa + cb) + g) : z4;
+        const float4 b1 = va ? __ldg(reinterpret_cast<const float4*>(rowa + cb) + 8 + g) : z4;
+        const float4 b2 = vb ? __ldg(reinterpret_cast<const float4*>(rowb + cb) + g) : z4;
+        const float4 b3 = vb ? __ldg(reinterpret_cast<const float4*>(rowb + cb) + 8 + g) : z4;
+        const float xa[2][4] = {{a0.x, a0.y, a0.z, a0.w}, {a1.x, a1.y, a1.z, a1.w}};
+        const float xb[2][8] = {{b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w},
+                                {b2.x, b2.y, b2.z, b2.w, b3.x, b3.y, b3.z, b3.w}};
+        uint32_t bigA[2][4], smlA[2][4], bigB[2][8], smlB[2][8];
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+          const bool valid = rr == 0 ? va : vb;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            float v = xa[rr][q];
+            if (CLIP) v = fminf(fmaxf(v, loa[q]), hia[q]);
+            v = valid ? v - ma[q] : 0.f;
+            bigA[rr][q] = to_tf32(v);
+            if (TERMS == 3) smlA[rr][q] = to_tf32(v - __uint_as_float(bigA[rr][q]));
+          }
+#pragma unroll
+          for (int jj = 0; jj < 8; ++jj) {
+            float v = xb[rr][jj];
+            if (CLIP) v = fminf(fmaxf(v, lob[jj]), hib[jj]);
+            v = valid ? v - mb[jj] : 0.f;
+            bigB[rr][jj] = to_tf32(v);
+            if (TERMS == 3) smlB[rr][jj] = to_tf32(v - __uint_as_float(bigB[rr][jj]));
+          }
+        }
+#pragma unroll
+        for (int il = 0; il < 2; ++il)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (TERMS == 3) {
+              mma_m16n8k8_tf32(acc[il][j], smlA[0][2 * il], smlA[0][2 * il + 1], smlA[1][2 * il], smlA[1][2 * il + 1], bigB[0][j], bigB[1][j]);
+              mma_m16n8k8_tf32(acc[il][j], bigA[0][2 * il], bigA[0][2 * il + 1], bigA[1][2 * il], bigA[1][2 * il + 1], smlB[0][j], smlB[1][j]);
+            }
+            mma_m16n8k8_tf32(acc[il][j], bigA[0][2 * il], bigA[0][2 * il + 1], bigA[1][2 * il], bigA[1][2 * il + 1], bigB[0][j], bigB[1][j]);
+          }
+      }
+#pragma unroll
+      for (int il = 0; il < 2; ++il)
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int Lm = 16 * (2 * hh + il) + g + ((e & 2) ? 8 : 0), Ln = 8 * j + 2 * t + (e & 1);
+            const int pm = ca + phys64(Lm), pn = cb + phys64(Ln);
+            G[(size_t)pm * D + pn] = acc[il][j][e];
+            G[(size_t)pn * D + pm] = acc[il][j][e];
+          }
+    }
+  }
+}
+
 // --------------------------------------------------------------------------------------------- generic, fp32
 constexpr int kGenRows = 16;
 
@@ -357,8 +553,25 @@ int launch_pass1(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws,
   const SubLayout& L = h->lay;
   if (L.nsub == 0) return SB_OK;
   const bool fast = h->d == 64 && !h->force_generic && (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
+  const bool blocked = (h->d == 128 || h->d == 256) && !h->force_generic && (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
   if (h->profile) cudaEventRecord(h->ev[0], st);
-  if (fast) {
+  if (blocked) {
+    const int per_sub = h->d == 256 ? 2 : 1;
+    int subs = L.nsub < kNumSMs * 2 ? L.nsub : kNumSMs * 2;
+    const int grid = subs * per_sub;
+#define SB_LAUNCH_BLOCKED(NB, THREADS)                                                                            \
+    do {                                                                                                          \
+      if (h->use_clip) {                                                                                          \
+        if (h->gram_terms == 3) pass1_gram_blocked_tf32<NB, true, 3><<<grid, THREADS, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials); \
+        else pass1_gram_blocked_tf32<NB, true, 1><<<grid, THREADS, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials);                    \
+      } else {                                                                                                    \
+        if (h->gram_terms == 3) pass1_gram_blocked_tf32<NB, false, 3><<<grid, THREADS, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials); \
+        else pass1_gram_blocked_tf32<NB, false, 1><<<grid, THREADS, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials);                   \
+      }                                                                                                           \
+    } while (0)
+    if (h->d == 256) SB_LAUNCH_BLOCKED(4, 256); else SB_LAUNCH_BLOCKED(2, 128);
+#undef SB_LAUNCH_BLOCKED
+  } else if (fast) {
     int grid = (int)ceil_div(L.nsub, 8);
     if (grid > kNumSMs) grid = kNumSMs;
     if (h->use_clip) {

@@ -118,6 +118,19 @@ def test_c2_shape_primed_then_scored(gram_terms, fused):
         assert abs(a["value"] - b["value"]) <= 1e-4 * max(abs(b["value"]), 1e-9), a["key"]
 
 
+@pytest.mark.parametrize("d", [128, 256])
+def test_wide_feature_tensor_paths(d):
+    """d = 128 / 256 (config 5 width): blocked Gram kernel + generalised projection kernel vs the fp64 oracle."""
+    prime, _ = synth.maha_rows_numpy(6000, d, 16, seed=51)
+    X, labels = synth.maha_rows_numpy(30001, d, 16, seed=52)
+    det, ref = OutlierMahalanobisB200(n_components=16), MahalanobisLean(n_components=16)
+    det.predict(prime, None), ref.predict(prime.astype(np.float64), None)
+    pg, pr = det.predict(X, None), ref.predict(X.astype(np.float64), None)
+    assert rel_err(det.score, ref.score).max() < TOL
+    assert np.array_equal(pg, pr) and np.array_equal(pr, labels.astype(int))
+    assert norm_err(det.C, ref.C) < TOL and norm_err(det.mean, ref.mean) < TOL
+
+
 def test_unconstrained_data_guard_band():
     """Plain N(0, Sigma) rows: flags must agree outside the |score - thr| <= 1e-4 thr band."""
     prime, _ = synth.maha_rows_numpy(30000, 64, 16, seed=21, unconstrained=True)
