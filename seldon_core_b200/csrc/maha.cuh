@@ -78,6 +78,7 @@ struct sb_maha {
   int stage;  // 0 idle, 1 pass1 done, 2 finalized, 3 scored
   int64_t rows_local, rows_total, row0, n_eff;
   int use_clip;
+  int split_pass2;  // decided in pass 1: projection kernel + chain kernel (d = 64/128/256, k <= 16, aligned rows)
   sb::SubLayout lay;
   // options
   int gram_terms, force_generic, profile, fused_pass2;

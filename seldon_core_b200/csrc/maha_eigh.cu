@@ -11,6 +11,8 @@
 // in parallel, one warp per pair, dot products by warp shuffles.  For 2*d*d*8 B <= 200 KB both matrices live
 // in shared memory (d <= 111), otherwise in the (L2-resident) workspace.  This is a latency kernel
 // (about 4*d^3 flops per sweep), not a roofline kernel; bench.py reports its time.
+#include <cooperative_groups.h>
+
 #include "maha.cuh"
 
 namespace sb {
@@ -135,6 +137,129 @@ jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, doub
   if (tid == 0) gate[3] = sweeps;
 }
 
+
+// d too large for one CTA's shared memory (d > 111): the same rotation scheme spread over several CTAs.  W and V live
+// in the workspace (1 MB at d = 256, L2 resident); every step the d/2 column pairs are rotated by one warp each
+// across the grid, and a cooperative grid barrier separates the steps.  Registers hold the two W and two V columns of
+// a pair (d/32 doubles per lane and column).
+template <int DMAX>
+__global__ void __launch_bounds__(256, 1)
+jacobi_topk_grid(const double* __restrict__ C, int d, int k, int KP, double* __restrict__ W, double* __restrict__ V,
+                 double* __restrict__ Vd, float* __restrict__ Vf, double* __restrict__ evals,
+                 long long* __restrict__ gate, double* __restrict__ Vfull, int warm, int* __restrict__ rot_flags) {
+  namespace cg = cooperative_groups;
+  cg::grid_group grid = cg::this_grid();
+  constexpr int PER = DMAX / 32;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31;
+  const int gwarp = tid >> 5, nwarp = nthr >> 5;
+  __shared__ double norms[kMaxD];
+
+  if (warm) {
+    for (int idx = tid; idx < d * d; idx += nthr) V[idx] = Vfull[idx];
+    grid.sync();
+    for (int idx = tid; idx < d * d; idx += nthr) {
+      const int c = idx / d, r = idx - c * d;
+      const double* crow = C + (size_t)r * d;
+      const double* vcol = V + (size_t)c * d;
+      double acc = 0.0;
+      for (int g = 0; g < d; ++g) acc = fma(crow[g], vcol[g], acc);
+      W[idx] = acc;
+    }
+  } else {
+    for (int idx = tid; idx < d * d; idx += nthr) {
+      const int c = idx / d, r = idx - c * d;
+      W[idx] = C[(size_t)r * d + c];
+      V[idx] = r == c ? 1.0 : 0.0;
+    }
+  }
+  if (tid < 64) rot_flags[tid] = 0;
+  grid.sync();
+  const int m = (d + 1) & ~1;
+  int sweeps = 0;
+  for (; sweeps < 40; ++sweeps) {
+    for (int step = 0; step < m - 1; ++step) {
+      for (int pr = gwarp; pr < m / 2; pr += nwarp) {
+        int p = pr == 0 ? m - 1 : (step + pr) % (m - 1);
+        int q = (step + m - 1 - pr) % (m - 1);
+        if (p >= d || q >= d) continue;
+        if (p > q) { int tmp = p; p = q; q = tmp; }
+        double* wp = W + (size_t)p * d;
+        double* wq = W + (size_t)q * d;
+        double a[PER], b[PER];
+        double al = 0.0, be = 0.0, ga = 0.0;
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+          const int r = lane + 32 * i;
+          a[i] = r < d ? __ldcg(wp + r) : 0.0;
+          b[i] = r < d ? __ldcg(wq + r) : 0.0;
+          al = fma(a[i], a[i], al);
+          be = fma(b[i], b[i], be);
+          ga = fma(a[i], b[i], ga);
+        }
+        al = warp_sum(al); be = warp_sum(be); ga = warp_sum(ga);
+        if (al == 0.0 || be == 0.0) continue;
+        if (ga * ga <= 1e-22 * (al * be)) continue;
+        const float zeta = __fdividef((float)(be - al), (float)(2.0 * ga));
+        const float tf = __fdividef(copysignf(1.f, zeta), fabsf(zeta) + sqrtf(fmaf(zeta, zeta, 1.f)));
+        if (!(fabsf(tf) > 0.f)) continue;
+        const double tt = (double)tf;
+        const double hh = fma(tt, tt, 1.0);
+        double cs = (double)rsqrtf((float)hh);
+        cs = cs * fma(-0.5 * hh, cs * cs, 1.5);
+        cs = cs * fma(-0.5 * hh, cs * cs, 1.5);
+        const double sn = cs * tt;
+        double* vp = V + (size_t)p * d;
+        double* vq = V + (size_t)q * d;
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+          const int r = lane + 32 * i;
+          if (r < d) {
+            __stcg(wp + r, cs * a[i] - sn * b[i]);
+            __stcg(wq + r, sn * a[i] + cs * b[i]);
+            const double x = __ldcg(vp + r), y = __ldcg(vq + r);
+            __stcg(vp + r, cs * x - sn * y);
+            __stcg(vq + r, sn * x + cs * y);
+          }
+        }
+        if (lane == 0) rot_flags[sweeps] = 1;
+      }
+      grid.sync();
+    }
+    if (__ldcg(rot_flags + sweeps) == 0) break;  // every thread reads the same flag after the barrier
+  }
+  // column norms, ranks and output by block 0 (small)
+  if (blockIdx.x == 0) {
+    const int warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int c = warp; c < d; c += nw) {
+      double acc = 0.0;
+      for (int r = lane; r < d; r += 32) { const double w = __ldcg(W + (size_t)c * d + r); acc = fma(w, w, acc); }
+      acc = warp_sum(acc);
+      if (lane == 0) norms[c] = sqrt(acc);
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < d * KP; idx += blockDim.x) {
+      const int c = idx % KP;
+      if (c >= k) { Vd[idx] = 0.0; Vf[idx] = 0.f; }
+    }
+    for (int c = threadIdx.x; c < d; c += blockDim.x) {
+      int rank = 0;
+      const double nc = norms[c];
+      for (int o = 0; o < d; ++o) rank += (norms[o] > nc) || (norms[o] == nc && o < c);
+      if (rank < k) {
+        evals[rank] = nc;
+        for (int f = 0; f < d; ++f) {
+          const double v = __ldcg(V + (size_t)c * d + f);
+          Vd[(size_t)f * KP + rank] = v;
+          Vf[(size_t)f * KP + rank] = (float)v;
+        }
+      }
+    }
+    if (threadIdx.x == 0) gate[3] = sweeps;
+  }
+  for (int idx = tid; idx < d * d; idx += nthr) Vfull[idx] = __ldcg(V + idx);
+}
+
 }  // namespace
 
 int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
@@ -148,8 +273,19 @@ int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
     jacobi_topk<true><<<1, 1024, need, st>>>(h->d_C1, d, h->k, h->KP, nullptr, nullptr, h->d_V, h->d_Vf, h->d_evals,
                                             h->d_gate, h->d_Vfull, warm);
   } else {
-    jacobi_topk<false><<<1, 1024, 0, st>>>(h->d_C1, d, h->k, h->KP, ws.eig_W, ws.eig_V, h->d_V, h->d_Vf, h->d_evals,
-                                           h->d_gate, h->d_Vfull, warm);
+    // cooperative multi-CTA solver: one warp per column pair
+    const int pairs = (d + 1) / 2;
+    int ctas = (int)ceil_div(pairs, 8);
+    if (ctas > kNumSMs) ctas = kNumSMs;
+    const double* Cp = h->d_C1;
+    int dd = d, kk = h->k, kp = h->KP, wm = warm;
+    double *Wp = ws.eig_W, *Vp = ws.eig_V, *Vdp = h->d_V, *evp = h->d_evals, *Vfl = h->d_Vfull;
+    float* Vfp = h->d_Vf;
+    long long* gp = h->d_gate;
+    int* flags = reinterpret_cast<int*>(h->d_gate + 8);
+    void* args[] = {&Cp, &dd, &kk, &kp, &Wp, &Vp, &Vdp, &Vfp, &evp, &gp, &Vfl, &wm, &flags};
+    if (d <= 256) SB_CUDA(cudaLaunchCooperativeKernel((void*)jacobi_topk_grid<256>, dim3(ctas), dim3(256), args, 0, st));
+    else SB_CUDA(cudaLaunchCooperativeKernel((void*)jacobi_topk_grid<512>, dim3(ctas), dim3(256), args, 0, st));
   }
   if (h->profile) cudaEventRecord(h->ev[3], st);
   SB_LAUNCH_CHECK();

@@ -118,11 +118,11 @@ extern "C" int32_t sb_maha_create(sb_maha_t** out, int32_t d, int32_t n_componen
   h->d_Vfull = p; p += dd;
   float* flt = nullptr;
   const size_t d4 = ((size_t)d + 3) & ~(size_t)3;  // keep every fp32 array 16-byte aligned
-  e = cudaMalloc(&flt, (3 * d4 + (size_t)d * KP) * sizeof(float) + 8 * sizeof(long long));
+  e = cudaMalloc(&flt, (3 * d4 + (size_t)d * KP) * sizeof(float) + 48 * sizeof(long long));
   if (e != cudaSuccess) { set_error("sb_maha_create: cudaMalloc: %s", cudaGetErrorString(e)); cudaFree(dbl); delete h; return SB_ERR_CUDA; }
-  cudaMemset(flt, 0, (3 * d4 + (size_t)d * KP) * sizeof(float) + 8 * sizeof(long long));
+  cudaMemset(flt, 0, (3 * d4 + (size_t)d * KP) * sizeof(float) + 48 * sizeof(long long));
   h->d_gate = (long long*)flt;  // 8-byte aligned slots first
-  float* q = flt + 16;
+  float* q = flt + 96;  // 48 eight-byte slots: counters [0,8), Jacobi sweep flags behind them
   h->d_mean_f = q; q += d4; h->d_lo_f = q; q += d4; h->d_hi_f = q; q += d4; h->d_Vf = q;
   *out = h;
   return SB_OK;
@@ -178,6 +178,8 @@ extern "C" int32_t sb_maha_pass1_stats(sb_maha_t* h, const float* d_X, int64_t r
   h->lay = make_layout(rows);
   h->n_eff = (h->max_n > 0 && h->n > h->max_n) ? h->max_n : h->n;  // CoreMahalanobis.py:79-82
   h->use_clip = (h->n > h->start_clip) && h->has_clip;               // L85 (uncapped n)
+  h->split_pass2 = h->KP == 16 && (h->d == 64 || h->d == 128 || h->d == 256) && !h->force_generic &&
+                   !h->fused_pass2 && (ld % 4 == 0) && (((uintptr_t)d_X & 15) == 0);
   if ((rc = launch_pass1(h, d_X, ld, ws, st))) return rc;
   if ((rc = launch_reduce(h, ws, d_stats_out ? d_stats_out : ws.stats, st))) return rc;
   h->stage = 1;
@@ -211,6 +213,8 @@ extern "C" int32_t sb_maha_pass2_score(sb_maha_t* h, const float* d_X, int64_t r
   SB_REQUIRE(h && d_X && d_score && d_flag && ld >= h->d, SB_ERR_INVALID, "sb_maha_pass2_score: bad arguments");
   SB_REQUIRE(h->stage == 2, SB_ERR_STATE, "sb_maha_pass2_score: call sb_maha_finalize first");
   SB_REQUIRE(rows == h->rows_local, SB_ERR_INVALID, "sb_maha_pass2_score: rows differ from pass 1");
+  SB_REQUIRE(!h->split_pass2 || ((ld % 4 == 0) && (((uintptr_t)d_X & 15) == 0)), SB_ERR_INVALID,
+             "sb_maha_pass2_score: X must have the alignment it had in pass 1");
   MahaWs ws;
   int rc = get_ws(h, rows, d_ws, ws_bytes, &ws);
   if (rc) return rc;

@@ -889,15 +889,20 @@ __host__ __device__ constexpr size_t proj_smem_bytes(int NB, bool clip) {
          + (size_t)NB * 16 * 32 * 16                  // B fragments
          + (clip ? (size_t)4 * kProjEvCap * 8 : 16)   // event lists, one per warp
          + (clip ? (size_t)4 * 16 * 16 * 4 : 16)      // y - z tiles, one per warp
-         + 64;                                        // event counters
+         + 64                                         // event counters
+         + (size_t)4 * 16 * 17 * 4;                   // z tiles for the Z^T Z fragments
 }
 
 // d = 64*NB, k <= 16.  Each warp projects blocks of 16 rows: 3xTF32 mma.sync over NB column chunks of 64 features.
+// A warp owns whole sub-segments, so it can also sum z and z z^T over each of them (Z^T Z on the tensor cores, same
+// 3xTF32 split): these are the projected sub-segment statistics that the prefix scan needs, i.e. V^T s and V^T G V of
+// the sub-segment without ever projecting a d x d partial.
 template <int NB, bool CLIP>
 __global__ void __launch_bounds__(128, NB == 1 ? 4 : 3)
-project_rows(const float* __restrict__ X, int64_t ld, int64_t rows, const float* __restrict__ mean_f,
+project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float* __restrict__ mean_f,
              const float* __restrict__ lo_f, const float* __restrict__ hi_f, const float* __restrict__ Vf,
-             float* __restrict__ Zout, float* __restrict__ Dout, uint8_t* __restrict__ cflag) {
+             float* __restrict__ Zout, float* __restrict__ Dout, uint8_t* __restrict__ cflag,
+             double* __restrict__ subproj) {
   constexpr int KP = 16, D = 64 * NB;
   extern __shared__ __align__(16) unsigned char proj_smem[];
   float* ms = reinterpret_cast<float*>(proj_smem);
@@ -908,10 +913,12 @@ project_rows(const float* __restrict__ X, int64_t ld, int64_t rows, const float*
   float2* evbase = reinterpret_cast<float2*>(vfrag + NB * 16 * 32);
   float* dtbase = reinterpret_cast<float*>(evbase + (CLIP ? 4 * kProjEvCap : 2));
   int* evcnt = reinterpret_cast<int*>(dtbase + (CLIP ? 4 * 16 * KP : 4));
+  float* ztbase = reinterpret_cast<float*>(evcnt + 16);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
   float2* evlist = evbase + (CLIP ? warp * kProjEvCap : 0);
   float* dt = dtbase + (CLIP ? warp * 16 * KP : 0);
+  float* zt = ztbase + warp * 16 * 17;  // this block's z, [row][comp] padded to 17
   for (int f = threadIdx.x; f < D; f += blockDim.x) {
     ms[f] = mean_f[f];
     los[f] = CLIP ? lo_f[f] : 0.f;
@@ -933,13 +940,12 @@ project_rows(const float* __restrict__ X, int64_t ld, int64_t rows, const float*
   if (threadIdx.x < 4) evcnt[threadIdx.x] = 0;
   __syncthreads();
 
-  const int64_t nblocks = (rows + 15) >> 4;
-  const int64_t wstride = (int64_t)gridDim.x * 4;
-  int64_t blk = (int64_t)blockIdx.x * 4 + warp;
+  const int64_t rows = lay.rows;
+  const int wtotal = gridDim.x * 4;
   float4 xa[4], xb[4];
-  auto load_rows = [&](int64_t b, int cc) {
-    const int64_t rb = b << 4;
-    const bool va = b < nblocks && rb + g < rows, vb8 = b < nblocks && rb + g + 8 < rows;
+  // rows [rb, rb+16) clipped to [.., rend): the loader of one 64-column chunk
+  auto load_rows = [&](int64_t rb, int64_t rend, int cc) {
+    const bool va = rb + g < rend, vb8 = rb + g + 8 < rend;
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
     const float4* pa = reinterpret_cast<const float4*>(X + (rb + g) * ld + 64 * cc);
     const float4* pb = reinterpret_cast<const float4*>(X + (rb + g + 8) * ld + 64 * cc);
@@ -949,10 +955,18 @@ project_rows(const float* __restrict__ X, int64_t ld, int64_t rows, const float*
       xb[q] = vb8 ? ldg_stream_f4(pb + 4 * q + t) : zero4;
     }
   };
-  load_rows(blk, 0);
-  for (; blk < nblocks; blk += wstride) {
-    const int64_t rb = blk << 4;
-    const bool va = rb + g < rows, vb8 = rb + g + 8 < rows;
+  for (int sub = blockIdx.x * 4 + warp; sub < lay.nsub; sub += wtotal) {
+  const int64_t r0 = sub_begin(lay, sub), r1 = sub_begin(lay, sub + 1);
+  float qacc[2][4], zsum[2][2];
+#pragma unroll
+  for (int nt = 0; nt < 2; ++nt) {
+    zsum[nt][0] = zsum[nt][1] = 0.f;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) qacc[nt][e] = 0.f;
+  }
+  load_rows(r0, r1, 0);
+  for (int64_t rb = r0; rb < r1; rb += 16) {
+    const bool va = rb + g < r1, vb8 = rb + g + 8 < r1;
     float accz[2][4];
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt)
@@ -966,8 +980,8 @@ project_rows(const float* __restrict__ X, int64_t ld, int64_t rows, const float*
         ra[q][0] = xa[q].x; ra[q][1] = xa[q].y; ra[q][2] = xa[q].z; ra[q][3] = xa[q].w;
         rbv[q][0] = xb[q].x; rbv[q][1] = xb[q].y; rbv[q][2] = xb[q].z; rbv[q][3] = xb[q].w;
       }
-      // next chunk (or the first chunk of the warp's next block) in flight while this one is multiplied
-      if (cc + 1 < NB) load_rows(blk, cc + 1); else load_rows(blk + wstride, 0);
+      // next chunk (or the first chunk of the next block of this sub-segment) in flight while this one is multiplied
+      if (cc + 1 < NB) load_rows(rb, r1, cc + 1); else load_rows(rb + 16, r1, 0);
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int cbase = 64 * cc + 16 * q + 4 * t;
@@ -1028,8 +1042,32 @@ project_rows(const float* __restrict__ X, int64_t ld, int64_t rows, const float*
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
       const int c0 = 8 * nt + 2 * t;
-      if (va) *reinterpret_cast<float2*>(Zout + (rb + g) * KP + c0) = make_float2(accz[nt][0], accz[nt][1]);
-      if (vb8) *reinterpret_cast<float2*>(Zout + (rb + g + 8) * KP + c0) = make_float2(accz[nt][2], accz[nt][3]);
+      // rows past the end of the sub-segment contribute nothing
+      const float z00 = va ? accz[nt][0] : 0.f, z01 = va ? accz[nt][1] : 0.f;
+      const float z10 = vb8 ? accz[nt][2] : 0.f, z11 = vb8 ? accz[nt][3] : 0.f;
+      if (va) *reinterpret_cast<float2*>(Zout + (rb + g) * KP + c0) = make_float2(z00, z01);
+      if (vb8) *reinterpret_cast<float2*>(Zout + (rb + g + 8) * KP + c0) = make_float2(z10, z11);
+      zsum[nt][0] += z00 + z10;
+      zsum[nt][1] += z01 + z11;
+      zt[g * 17 + c0] = z00; zt[g * 17 + c0 + 1] = z01;
+      zt[(g + 8) * 17 + c0] = z10; zt[(g + 8) * 17 + c0 + 1] = z11;
+    }
+    __syncwarp();
+    // Q += Z^T Z over the 16 rows: A[m = comp][k = row] and B[k = row][n = comp] are the same four values per step
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks) {
+      const float f0 = zt[(8 * ks + t) * 17 + g], f1 = zt[(8 * ks + t) * 17 + g + 8];
+      const float f2 = zt[(8 * ks + t + 4) * 17 + g], f3 = zt[(8 * ks + t + 4) * 17 + g + 8];
+      const uint32_t b0 = to_tf32(f0), b1 = to_tf32(f1), b2 = to_tf32(f2), b3 = to_tf32(f3);
+      const uint32_t s0 = to_tf32(f0 - __uint_as_float(b0)), s1 = to_tf32(f1 - __uint_as_float(b1));
+      const uint32_t s2 = to_tf32(f2 - __uint_as_float(b2)), s3 = to_tf32(f3 - __uint_as_float(b3));
+      // n-tile 0 uses (k=t, n=g) = f0 and (k=t+4, n=g) = f2; n-tile 1 uses f1, f3
+      mma_m16n8k8_tf32(qacc[0], s0, s1, s2, s3, b0, b2);
+      mma_m16n8k8_tf32(qacc[0], b0, b1, b2, b3, s0, s2);
+      mma_m16n8k8_tf32(qacc[0], b0, b1, b2, b3, b0, b2);
+      mma_m16n8k8_tf32(qacc[1], s0, s1, s2, s3, b1, b3);
+      mma_m16n8k8_tf32(qacc[1], b0, b1, b2, b3, s1, s3);
+      mma_m16n8k8_tf32(qacc[1], b0, b1, b2, b3, b1, b3);
     }
     unsigned rowmask = 0;
     if (CLIP) {
@@ -1052,7 +1090,7 @@ project_rows(const float* __restrict__ X, int64_t ld, int64_t rows, const float*
           // more than kProjEvCap clipped elements in 16 rows (degenerate data): recompute the block densely
           rowmask = 0xffffu;
           for (int row = half; row < 16; row += 2) {
-            if (rb + row >= rows) break;
+            if (rb + row >= r1) break;
             const float* xr = X + (rb + row) * ld;
             float acc = 0.f;
             for (int f = 0; f < D; ++f) {
@@ -1070,9 +1108,31 @@ project_rows(const float* __restrict__ X, int64_t ld, int64_t rows, const float*
         if (lane == 0) evcnt[warp] = 0;
       }
     }
-    if (lane < 16 && rb + lane < rows) cflag[rb + lane] = (uint8_t)((rowmask >> lane) & 1u);
+    if (lane < 16 && rb + lane < r1) cflag[rb + lane] = (uint8_t)((rowmask >> lane) & 1u);
     __syncwarp();
   }
+  // projected statistics of this sub-segment: sum z (16) and sum z z^T (16 x 16)
+  {
+    double* o = subproj + (size_t)sub * (KP + KP * KP);
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+#pragma unroll
+      for (int h2 = 0; h2 < 2; ++h2) {
+        float v = zsum[nt][h2];
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        if (g == 0) o[8 * nt + 2 * t + h2] = (double)v;
+      }
+      const int n0 = 8 * nt + 2 * t;
+      o[KP + g * KP + n0] = (double)qacc[nt][0];
+      o[KP + g * KP + n0 + 1] = (double)qacc[nt][1];
+      o[KP + (g + 8) * KP + n0] = (double)qacc[nt][2];
+      o[KP + (g + 8) * KP + n0 + 1] = (double)qacc[nt][3];
+    }
+  }
+  }
+  (void)rows;
 }
 
 // chain over the projected rows: group of 16 lanes per sub-segment, lane j owns row j of S^-1.
@@ -1282,9 +1342,14 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
   int grid = nsub < kNumSMs * 8 ? nsub : kNumSMs * 8;
   const int FC = d < 8192 / d ? d : 8192 / d;
   const size_t sp_smem = ((((size_t)FC * d + 3) & ~(size_t)3) + (size_t)FC * KP) * sizeof(float);
-  sub_project<float><<<grid, 256, sp_smem, st>>>(ws.partials, PS, nsub, d, KP, h->d_Vf, ws.subproj);
-  SB_LAUNCH_CHECK();
   sub_project<double><<<1, 256, sp_smem, st>>>(ws.rank_pre + 1, PS, 1, d, KP, h->d_Vf, rank_proj);
+  SB_LAUNCH_CHECK();
+  if (h->split_pass2) {
+    // the projection kernel of pass 2 produces the per-sub-segment statistics; scan and start inverses follow it
+    if (h->profile) cudaEventRecord(h->ev[5], st);
+    return SB_OK;
+  }
+  sub_project<float><<<grid, 256, sp_smem, st>>>(ws.partials, PS, nsub, d, KP, h->d_Vf, ws.subproj);
   SB_LAUNCH_CHECK();
   const int nchunk = (int)ceil_div(nsub, kScanChunk);
   sub_scan_totals<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
@@ -1305,6 +1370,43 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
                     cudaStream_t st) {
   const int d = h->d, nsub = h->lay.nsub;
   const SubLayout& L = h->lay;
+  const bool aligned = (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
+  const bool fast = KP == 16 && d == 64 && !h->force_generic && aligned;
+  const bool split = h->split_pass2 != 0;
+  if (h->profile) { cudaEventRecord(h->ev[6], st); cudaEventRecord(h->ev[7], st); }
+  if (split) {
+    // projection (z, clip correction, per-sub-segment sums) -> scan -> start inverses -> gate
+    const int NBv = d / 64;
+    int pgrid = (int)ceil_div(nsub, 4);
+    const int pmax = kNumSMs * (NBv == 1 ? 4 : 3);
+    if (pgrid > pmax) pgrid = pmax;
+#define SB_LAUNCH_PROJECT(NB, CLIPV)                                                                               \
+    do {                                                                                                           \
+      const size_t psm = proj_smem_bytes(NB, CLIPV);                                                               \
+      SB_CUDA(cudaFuncSetAttribute(project_rows<NB, CLIPV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psm)); \
+      project_rows<NB, CLIPV><<<pgrid, 128, psm, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf,       \
+                                                      ws.proj_Z, ws.proj_D, ws.proj_flag, ws.subproj);             \
+    } while (0)
+    if (h->use_clip) {
+      if (NBv == 1) SB_LAUNCH_PROJECT(1, true); else if (NBv == 2) SB_LAUNCH_PROJECT(2, true); else SB_LAUNCH_PROJECT(4, true);
+    } else {
+      if (NBv == 1) SB_LAUNCH_PROJECT(1, false); else if (NBv == 2) SB_LAUNCH_PROJECT(2, false); else SB_LAUNCH_PROJECT(4, false);
+    }
+#undef SB_LAUNCH_PROJECT
+    SB_LAUNCH_CHECK();
+    if (h->profile) cudaEventRecord(h->ev[7], st);
+    constexpr int KQ = KP + KP * KP;
+    const int nchunk = (int)ceil_div(nsub, kScanChunk);
+    sub_scan_totals<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
+    SB_LAUNCH_CHECK();
+    sub_scan_apply<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot, ws.rank_proj);
+    SB_LAUNCH_CHECK();
+    sub_start<KP><<<(int)ceil_div(nsub, 4), 128, 0, st>>>(ws.subproj, h->d_PC0, L, h->k, (long long)h->n_eff,
+                                                         (long long)h->row0, ws.sub_P, ws.sub_Z, ws.sub_flags);
+    SB_LAUNCH_CHECK();
+    gate_init<<<1, 32, 0, st>>>(ws.sub_flags, L, (long long)h->row0, h->d_gate, h->d_score_sum);
+    SB_LAUNCH_CHECK();
+  }
   // exact fp64 warm-up path (does nothing in the steady state: b* = 0 and every start is well conditioned)
   {
     int grid = nsub < kNumSMs * 16 ? nsub : kNumSMs * 16;
@@ -1323,52 +1425,33 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
                                    flag);
     SB_LAUNCH_CHECK();
   }
-  const bool aligned = (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
-  const bool fast = KP == 16 && d == 64 && !h->force_generic && aligned;
-  const bool split = KP == 16 && (d == 64 || d == 128 || d == 256) && !h->force_generic && aligned && !h->fused_pass2;
-  if (h->profile) { cudaEventRecord(h->ev[6], st); cudaEventRecord(h->ev[7], st); cudaEventRecord(h->ev[8], st); }
+  if (h->profile) cudaEventRecord(h->ev[8], st);
   if (split) {
-    const int64_t nblocks = ceil_div(h->rows_local, 16);
-    const int NBv = d / 64;
-    int pgrid = (int)ceil_div(nblocks, 4);
-    const int pmax = kNumSMs * (NBv == 1 ? 4 : 3);
-    if (pgrid > pmax) pgrid = pmax;
-    int cgrid = (int)ceil_div(nsub, 16);
-    if (cgrid > kNumSMs * 2) cgrid = kNumSMs * 2;
-#define SB_LAUNCH_PROJECT(NB, CLIPV)                                                                               \
-    do {                                                                                                           \
-      const size_t psm = proj_smem_bytes(NB, CLIPV);                                                               \
-      SB_CUDA(cudaFuncSetAttribute(project_rows<NB, CLIPV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psm)); \
-      project_rows<NB, CLIPV><<<pgrid, 128, psm, st>>>(X, ld, h->rows_local, h->d_mean_f, h->d_lo_f, h->d_hi_f,    \
-                                                      h->d_Vf, ws.proj_Z, ws.proj_D, ws.proj_flag);                \
-    } while (0)
-    if (h->use_clip) {
-      if (NBv == 1) SB_LAUNCH_PROJECT(1, true); else if (NBv == 2) SB_LAUNCH_PROJECT(2, true); else SB_LAUNCH_PROJECT(4, true);
-      SB_LAUNCH_CHECK();
-      if (h->profile) { cudaEventRecord(h->ev[7], st); cudaEventRecord(h->ev[8], st); }
-      chain16<true><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
-                                          (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
-                                          h->d_score_sum, score, flag);
-    } else {
-      if (NBv == 1) SB_LAUNCH_PROJECT(1, false); else if (NBv == 2) SB_LAUNCH_PROJECT(2, false); else SB_LAUNCH_PROJECT(4, false);
-      SB_LAUNCH_CHECK();
-      if (h->profile) { cudaEventRecord(h->ev[7], st); cudaEventRecord(h->ev[8], st); }
-      chain16<false><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
-                                           (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
-                                           h->d_score_sum, score, flag);
+    if constexpr (KP == 16) {
+      int cgrid = (int)ceil_div(nsub, 16);
+      if (cgrid > kNumSMs * 2) cgrid = kNumSMs * 2;
+      if (h->use_clip)
+        chain16<true><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
+                                            (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
+                                            h->d_score_sum, score, flag);
+      else
+        chain16<false><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
+                                             (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
+                                             h->d_score_sum, score, flag);
     }
-#undef SB_LAUNCH_PROJECT
   } else if (fast) {
-    int grid = (int)ceil_div(nsub, 8);
-    if (grid > kNumSMs * 3) grid = kNumSMs * 3;
-    if (h->use_clip)
-      score_chain64<true><<<grid, 128, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf, ws.sub_P,
-                                               ws.sub_Z, ws.sub_flags, (long long)h->n_eff, (long long)h->row0,
-                                               h->threshold, h->d_gate, h->d_score_sum, score, flag);
-    else
-      score_chain64<false><<<grid, 128, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf, ws.sub_P,
-                                                ws.sub_Z, ws.sub_flags, (long long)h->n_eff, (long long)h->row0,
-                                                h->threshold, h->d_gate, h->d_score_sum, score, flag);
+    if constexpr (KP == 16) {
+      int grid = (int)ceil_div(nsub, 8);
+      if (grid > kNumSMs * 3) grid = kNumSMs * 3;
+      if (h->use_clip)
+        score_chain64<true><<<grid, 128, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf, ws.sub_P,
+                                                 ws.sub_Z, ws.sub_flags, (long long)h->n_eff, (long long)h->row0,
+                                                 h->threshold, h->d_gate, h->d_score_sum, score, flag);
+      else
+        score_chain64<false><<<grid, 128, 0, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf, ws.sub_P,
+                                                  ws.sub_Z, ws.sub_flags, (long long)h->n_eff, (long long)h->row0,
+                                                  h->threshold, h->d_gate, h->d_score_sum, score, flag);
+    }
   } else {
     const int groups_per_cta = 128 / KP;
     int grid = (int)ceil_div(nsub, groups_per_cta);
