@@ -146,11 +146,13 @@ int32_t sb_maha_get_eigvecs(sb_maha_t* h, double* h_V, uintptr_t stream);
 /* tuning knobs: SB_OPT_GRAM_TERMS 1|3 (TF32 products per Gram element, default 3),
  * SB_OPT_FORCE_GENERIC 0|1 (skip the d=64 tensor-core kernels), SB_OPT_PROFILE 0|1 (record CUDA events around
  * the main kernels on the caller's stream), SB_OPT_FUSED_PASS2 0|1 (d=64: project and chain in one kernel instead
- * of the default projection kernel + chain kernel) */
+ * of the default projection kernel + chain kernel), SB_OPT_LEGACY_MMA 0|1 (pass-1 Gram on mma.sync instead of the
+ * default tcgen05.mma kernel) */
 #define SB_OPT_GRAM_TERMS 1
 #define SB_OPT_FORCE_GENERIC 2
 #define SB_OPT_PROFILE 3
 #define SB_OPT_FUSED_PASS2 4
+#define SB_OPT_LEGACY_MMA 5
 int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t value);
 /* number of kernel launches issued through this handle so far (bench.py's gpu_launches) */
 int64_t sb_launch_count(void);

@@ -57,6 +57,7 @@ struct MahaWs {  // device pointers carved out of the caller's workspace
 };
 
 int reduce_slices(int d);
+int launch_pass1_umma(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws, cudaStream_t st);
 int launch_pass1(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws, cudaStream_t st);
 int launch_reduce(const sb_maha* h, const MahaWs& ws, double* stats_out, cudaStream_t st);
 int launch_finalize_cov(sb_maha* h, const double* all_stats, int nranks, int rank, const MahaWs& ws, cudaStream_t st);
@@ -81,7 +82,7 @@ struct sb_maha {
   int split_pass2;  // decided in pass 1: projection kernel + chain kernel (d = 64/128/256, k <= 16, aligned rows)
   sb::SubLayout lay;
   // options
-  int gram_terms, force_generic, profile, fused_pass2;
+  int gram_terms, force_generic, profile, fused_pass2, legacy_mma;
   cudaEvent_t ev[10];  // profile: [0,1] pass-1 kernel, [2,3] eigh, [4,5] prefix kernels, [6,7] projection, [8,9] chain
   // device state
   double *d_mean, *d_C, *d_lo, *d_hi;      // committed

@@ -1,0 +1,350 @@
+// Mahalanobis pass 1 on the 5th-generation tensor cores: the Gram statistics as a tcgen05.mma contraction.
+//
+// Replaces CoreMahalanobis.py:98-100 of the reference (the (nb,p,p) outer-product tensor and its sum) for
+// d = 64, 128 and 256: per sub-segment  s = sum(xc - a),  G = sum (xc - a)(xc - a)^T  (see maha_stats.cu).
+//
+// Data flow per CTA (one per SM, persistent over sub-segments), 128 threads:
+//   global --LDG.128 (128 contiguous bytes per row and warp instruction)--> registers: clip, subtract the start-of-call
+//   mean, split every value into a TF32 "hi" part and the TF32-rounded remainder "lo"  --STS.128--> two shared-memory
+//   tiles T_hi, T_lo of 32 rows x D features in the canonical MN-major tf32 layout (SWIZZLE_128B_BASE32B: 128-byte
+//   feature slabs, 4-row atoms, 32-byte chunks XOR-ed with row & 3; verified on hardware with tools/umma_probe.cu)
+//   --tcgen05.mma.kind::tf32, A = B = the same tile (the Gram is T^T T)--> fp32 accumulator in TMEM
+//   (3 MMAs per 8 rows: hi*hi + hi*lo + lo*hi = the 3xTF32 product with fp32-level accuracy).
+// A ring of 3 tile pairs lets the loads/splits of chunk c+1.. overlap the MMAs of chunk c; tcgen05.commit releases a
+// ring slot through an mbarrier.  At the end of a sub-segment the accumulator is read back with tcgen05.ld and stored
+// as the sub-segment's partial.  d = 256 uses two accumulators (rows 0-127 x 256 columns, rows 128-255 x columns
+// 128-255: the block below the diagonal is mirrored on store), 384 of the 512 TMEM columns.
+//
+// Bounds: d = 64: the tiles are read twice per MMA (A and B) so shared-memory bandwidth, not HBM, is the limiter at
+// roughly 0.7 of the HBM rate; d = 256: tensor pipe (2*d*d*0.75*3 flop per row).
+#include "maha.cuh"
+
+namespace sb {
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  }
+}
+
+// shared-memory matrix descriptor: MN-major tf32 tile, layout SWIZZLE_128B_BASE32B (= 1), descriptor version 1
+__device__ __forceinline__ uint64_t umma_desc(uint32_t start, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((start >> 4) & 0x3fff) | ((uint64_t)((lbo >> 4) & 0x3fff) << 16) |
+         ((uint64_t)((sbo >> 4) & 0x3fff) << 32) | (1ull << 46) | (1ull << 61);
+}
+
+// instruction descriptor: D = fp32, A = B = tf32, both MN-major, shape M x N (K = 8)
+__host__ __device__ constexpr uint32_t umma_idesc(int M, int N) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc),
+      "r"(accum) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,"
+      "%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];\n\t"
+      "tcgen05.wait::ld.sync.aligned;"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+
+constexpr int kUmmaStages = 3;
+constexpr int kChunkRows = 32;
+
+__host__ __device__ constexpr size_t umma_smem_bytes(int D, int terms) {
+  return (size_t)kUmmaStages * (terms == 3 ? 2 : 1) * kChunkRows * D * 4 + (size_t)3 * D * 4 + 1024 /* alignment slack */;
+}
+
+template <int D, bool CLIP, int TERMS>
+__global__ void __launch_bounds__(128, 1)
+pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const float* __restrict__ mean_f,
+                const float* __restrict__ lo_f, const float* __restrict__ hi_f, float* __restrict__ partials) {
+  constexpr int PS = D + D * D;
+  constexpr int NSLAB = D / 32;                 // 128-byte feature slabs per row
+  constexpr uint32_t LBO = 512;                 // between feature slabs of one 4-row atom
+  constexpr uint32_t SBO = NSLAB * 512;         // between 4-row groups
+  constexpr int TILE = kChunkRows * D * 4;      // bytes of one 32 x D tile
+  constexpr int NT = TERMS == 3 ? 2 : 1;        // tiles per stage (hi, lo)
+  constexpr int NPIECE = D / 32;                // float4 pieces per thread and row set: lane&7 + 8*i
+  constexpr int TMEM_COLS = D == 256 ? 512 : D; // power of two >= columns used (D = 256 uses 384)
+  extern __shared__ uint8_t umma_smem_raw[];
+  uint8_t* tiles = (uint8_t*)(((uintptr_t)umma_smem_raw + 1023) & ~(uintptr_t)1023);
+  float* ms = reinterpret_cast<float*>(tiles + kUmmaStages * NT * TILE);
+  float* los = ms + D;
+  float* his = los + D;
+  __shared__ uint64_t bar_empty[kUmmaStages];
+  __shared__ uint64_t bar_acc;
+  __shared__ uint32_t tmem_base_s;
+  __shared__ float ssum_s[D];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int rsub = lane >> 3, piece0 = lane & 7;  // 4 rows x 8 pieces (128 contiguous bytes of a row) per warp instruction
+  for (int f = tid; f < D; f += blockDim.x) {
+    ms[f] = mean_f[f];
+    los[f] = CLIP ? lo_f[f] : 0.f;
+    his[f] = CLIP ? hi_f[f] : 0.f;
+  }
+  if (tid == 0) {
+    for (int s = 0; s < kUmmaStages; ++s)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar_empty[s])));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar_acc)));
+    asm volatile("fence.mbarrier_init.release.cluster;");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;");
+  const uint32_t tmem = tmem_base_s;
+  const uint32_t tiles_u32 = smem_u32(tiles);
+
+  uint32_t it = 0;        // chunks issued so far by this CTA (ring position)
+  uint32_t acc_parity = 0;
+  for (int sub = blockIdx.x; sub < lay.nsub; sub += gridDim.x) {
+    const int64_t r0 = sub_begin(lay, sub), r1 = sub_begin(lay, sub + 1);
+    const int nchunks = (int)((r1 - r0 + kChunkRows - 1) / kChunkRows);
+    float4 sums[2][NPIECE];
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+#pragma unroll
+      for (int i = 0; i < NPIECE; ++i) sums[h][i] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+    // rows of a chunk handled by this thread: 8*warp + rsub and 8*warp + 4 + rsub
+    float4 cur[2][NPIECE];
+    auto load_chunk = [&](int c, float4 (&v)[2][NPIECE]) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int64_t row = r0 + (int64_t)c * kChunkRows + 8 * warp + 4 * h + rsub;
+        const bool valid = row < r1;
+        const float4* p = reinterpret_cast<const float4*>(X + row * ld);
+#pragma unroll
+        for (int i = 0; i < NPIECE; ++i) v[h][i] = valid ? ldg_stream_f4(p + piece0 + 8 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    };
+    if (nchunks > 0) load_chunk(0, cur);
+    for (int c = 0; c < nchunks; ++c, ++it) {
+      const uint32_t stage = it % kUmmaStages;
+      uint8_t* th = tiles + (size_t)stage * NT * TILE;  // hi tile; lo tile follows
+      if (it >= (uint32_t)kUmmaStages) mbar_wait(smem_u32(&bar_empty[stage]), ((it / kUmmaStages) - 1) & 1);
+      float4 nxt[2][NPIECE];
+      if (c + 1 < nchunks) load_chunk(c + 1, nxt);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int k = 8 * warp + 4 * h + rsub;  // row inside the chunk
+        const bool valid = r0 + (int64_t)c * kChunkRows + k < r1;
+#pragma unroll
+        for (int i = 0; i < NPIECE; ++i) {
+          const int piece = piece0 + 8 * i;      // float4 index inside the row: features 4*piece .. 4*piece+3
+          const float4 m4 = *reinterpret_cast<const float4*>(ms + 4 * piece);
+          float v[4] = {cur[h][i].x, cur[h][i].y, cur[h][i].z, cur[h][i].w};
+          const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
+          if (CLIP) {
+            const float4 l4 = *reinterpret_cast<const float4*>(los + 4 * piece);
+            const float4 h4 = *reinterpret_cast<const float4*>(his + 4 * piece);
+            const float ll[4] = {l4.x, l4.y, l4.z, l4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) v[e] = fminf(fmaxf(v[e], ll[e]), hh[e]);
+          }
+          uint32_t hi4[4], lo4[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float dv = valid ? v[e] - mm[e] : 0.f;
+            hi4[e] = to_tf32(dv);
+            if (TERMS == 3) lo4[e] = to_tf32(dv - __uint_as_float(hi4[e]));
+            v[e] = dv;
+          }
+          sums[h][i].x += v[0]; sums[h][i].y += v[1]; sums[h][i].z += v[2]; sums[h][i].w += v[3];
+          // canonical address of (row k, features 4*piece..): slab = piece >> 3, byte in the 128-byte row b = 16*(piece&7)
+          const uint32_t b = 16u * (piece & 7);
+          const uint32_t off = (uint32_t)(k >> 2) * SBO + (uint32_t)(piece >> 3) * LBO + (uint32_t)(k & 3) * 128u +
+                               ((((b >> 5) ^ (uint32_t)(k & 3)) << 5) | (b & 31u));
+          *reinterpret_cast<uint4*>(th + off) = make_uint4(hi4[0], hi4[1], hi4[2], hi4[3]);
+          if (TERMS == 3) *reinterpret_cast<uint4*>(th + TILE + off) = make_uint4(lo4[0], lo4[1], lo4[2], lo4[3]);
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the tensor core
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncthreads();
+      if (tid == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t hbase = tiles_u32 + stage * NT * TILE, lbase = hbase + TILE;
+#pragma unroll
+        for (int ks = 0; ks < kChunkRows / 8; ++ks) {
+          const uint32_t koff = (uint32_t)ks * 2u * SBO;  // 8 rows = two 4-row groups
+          const uint32_t first = (c > 0 || ks > 0) ? 1u : 0u;
+          if (D <= 128) {
+            constexpr uint32_t idesc = umma_idesc(D, D);
+            const uint64_t dh = umma_desc(hbase + koff, LBO, SBO), dl = umma_desc(lbase + koff, LBO, SBO);
+            umma_tf32(tmem, dh, dh, idesc, first);
+            if (TERMS == 3) {
+              umma_tf32(tmem, dh, dl, idesc, 1u);
+              umma_tf32(tmem, dl, dh, idesc, 1u);
+            }
+          } else {
+            // rows 0-127 against all 256 columns -> TMEM columns [0,256); rows 128-255 against columns 128-255 -> [256,384)
+            constexpr uint32_t id0 = umma_idesc(128, 256), id1 = umma_idesc(128, 128);
+            const uint64_t dh0 = umma_desc(hbase + koff, LBO, SBO), dl0 = umma_desc(lbase + koff, LBO, SBO);
+            const uint64_t dh1 = umma_desc(hbase + koff + 4 * LBO, LBO, SBO), dl1 = umma_desc(lbase + koff + 4 * LBO, LBO, SBO);
+            umma_tf32(tmem, dh0, dh0, id0, first);
+            umma_tf32(tmem + 256, dh1, dh1, id1, first);
+            if (TERMS == 3) {
+              umma_tf32(tmem, dh0, dl0, id0, 1u);
+              umma_tf32(tmem, dl0, dh0, id0, 1u);
+              umma_tf32(tmem + 256, dh1, dl1, id1, 1u);
+              umma_tf32(tmem + 256, dl1, dh1, id1, 1u);
+            }
+          }
+        }
+        // the ring slot is free again once these MMAs have read it
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar_empty[stage])) : "memory");
+        if (c == nchunks - 1)
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar_acc)) : "memory");
+      }
+      if (c + 1 < nchunks) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+          for (int i = 0; i < NPIECE; ++i) cur[h][i] = nxt[h][i];
+      }
+    }
+
+    // ---- end of the sub-segment: row sums, then the accumulator
+    float* part = partials + (size_t)sub * PS;
+    for (int f = tid; f < D; f += blockDim.x) ssum_s[f] = 0.f;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < NPIECE; ++i) {
+      float4 a = sums[0][i];
+      a.x += sums[1][i].x; a.y += sums[1][i].y; a.z += sums[1][i].z; a.w += sums[1][i].w;
+      // lanes with the same piece0 hold different rows: reduce over rsub (lane bits 3,4)
+#pragma unroll
+      for (int o = 8; o <= 16; o <<= 1) {
+        a.x += __shfl_xor_sync(0xffffffffu, a.x, o);
+        a.y += __shfl_xor_sync(0xffffffffu, a.y, o);
+        a.z += __shfl_xor_sync(0xffffffffu, a.z, o);
+        a.w += __shfl_xor_sync(0xffffffffu, a.w, o);
+      }
+      if (rsub == 0) {
+        const int f = 4 * (piece0 + 8 * i);
+        atomicAdd(&ssum_s[f], a.x); atomicAdd(&ssum_s[f + 1], a.y); atomicAdd(&ssum_s[f + 2], a.z); atomicAdd(&ssum_s[f + 3], a.w);
+      }
+    }
+    __syncthreads();
+    for (int f = tid; f < D; f += blockDim.x) part[f] = ssum_s[f];
+
+    float* G = part + D;
+    if (nchunks > 0) {
+      mbar_wait(smem_u32(&bar_acc), acc_parity);
+      acc_parity ^= 1u;
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      uint32_t r[32];
+      if (D == 64) {
+        // M = 64: accumulator row m sits in TMEM lane (m & 15) + 32 * (m >> 4): lanes 0-15 of every warp's quarter
+#pragma unroll
+        for (int c0 = 0; c0 < 64; c0 += 32) {
+          tmem_ld32(tmem + ((uint32_t)(32 * warp) << 16) + c0, r);
+          if (lane < 16) {
+            float4* dst = reinterpret_cast<float4*>(G + (size_t)(16 * warp + lane) * D + c0);
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]), __uint_as_float(r[4 * q + 2]),
+                                   __uint_as_float(r[4 * q + 3]));
+          }
+        }
+      } else {
+        const int m = 32 * warp + lane;  // M = 128: row m in lane m
+        constexpr int NC0 = D == 256 ? 256 : D;
+#pragma unroll 1
+        for (int c0 = 0; c0 < NC0; c0 += 32) {
+          tmem_ld32(tmem + ((uint32_t)(32 * warp) << 16) + c0, r);
+          float4* dst = reinterpret_cast<float4*>(G + (size_t)m * D + c0);
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]), __uint_as_float(r[4 * q + 2]),
+                                 __uint_as_float(r[4 * q + 3]));
+          if (D == 256 && c0 >= 128) {  // mirror the block above the diagonal into rows 128-255, columns 0-127
+#pragma unroll
+            for (int e = 0; e < 32; ++e) G[(size_t)(c0 + e) * D + m] = __uint_as_float(r[e]);
+          }
+        }
+        if (D == 256) {
+#pragma unroll 1
+          for (int c0 = 0; c0 < 128; c0 += 32) {
+            tmem_ld32(tmem + ((uint32_t)(32 * warp) << 16) + 256 + c0, r);
+            float4* dst = reinterpret_cast<float4*>(G + (size_t)(128 + m) * D + 128 + c0);
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]), __uint_as_float(r[4 * q + 2]),
+                                   __uint_as_float(r[4 * q + 3]));
+          }
+        }
+      }
+    } else {
+      for (int e = tid; e < D * D; e += blockDim.x) G[e] = 0.f;
+    }
+    // every warp has drained its lanes before the next sub-segment's first MMA overwrites the accumulator
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS));
+  }
+}
+
+template <int D>
+int launch_umma_d(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws, cudaStream_t st) {
+  const SubLayout& L = h->lay;
+  int grid = L.nsub < kNumSMs ? L.nsub : kNumSMs;
+#define SB_UMMA_LAUNCH(CLIPV, TERMSV)                                                                                   \
+  do {                                                                                                                  \
+    const size_t smem = umma_smem_bytes(D, TERMSV);                                                                     \
+    SB_CUDA(cudaFuncSetAttribute(pass1_gram_umma<D, CLIPV, TERMSV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    pass1_gram_umma<D, CLIPV, TERMSV><<<grid, 128, smem, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials); \
+  } while (0)
+  if (h->use_clip) {
+    if (h->gram_terms == 3) SB_UMMA_LAUNCH(true, 3); else SB_UMMA_LAUNCH(true, 1);
+  } else {
+    if (h->gram_terms == 3) SB_UMMA_LAUNCH(false, 3); else SB_UMMA_LAUNCH(false, 1);
+  }
+#undef SB_UMMA_LAUNCH
+  return SB_OK;
+}
+
+}  // namespace
+
+// returns SB_OK after launching, or 1 if this shape is not handled by the tcgen05 kernel
+int launch_pass1_umma(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws, cudaStream_t st) {
+  if (ld % 4 != 0 || ((uintptr_t)X & 15) != 0) return 1;
+  switch (h->d) {
+    case 64: return launch_umma_d<64>(h, X, ld, ws, st);
+    case 128: return launch_umma_d<128>(h, X, ld, ws, st);
+    case 256: return launch_umma_d<256>(h, X, ld, ws, st);
+  }
+  return 1;
+}
+
+}  // namespace sb

@@ -153,6 +153,8 @@ extern "C" int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t valu
     h->gram_terms = (int)value;
   } else if (option == SB_OPT_FORCE_GENERIC) {
     h->force_generic = value != 0;
+  } else if (option == SB_OPT_LEGACY_MMA) {
+    h->legacy_mma = value != 0;
   } else if (option == SB_OPT_FUSED_PASS2) {
     h->fused_pass2 = value != 0;
   } else if (option == SB_OPT_PROFILE) {

@@ -555,7 +555,14 @@ int launch_pass1(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws,
   const bool fast = h->d == 64 && !h->force_generic && (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
   const bool blocked = (h->d == 128 || h->d == 256) && !h->force_generic && (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
   if (h->profile) cudaEventRecord(h->ev[0], st);
-  if (blocked) {
+  int umma_rc = 1;
+  if (!h->force_generic && !h->legacy_mma) {
+    umma_rc = launch_pass1_umma(h, X, ld, ws, st);  // tcgen05 path for d = 64 / 128 / 256
+    if (umma_rc < 0) return umma_rc;
+  }
+  if (umma_rc == SB_OK) {
+    // launched above
+  } else if (blocked) {
     const int per_sub = h->d == 256 ? 2 : 1;
     int subs = L.nsub < kNumSMs * 2 ? L.nsub : kNumSMs * 2;
     const int grid = subs * per_sub;

@@ -54,15 +54,17 @@ def check_batch(det, ref_score, ref_pred, n_before, k, label):
     return int(err[strict].size)
 
 
-@pytest.mark.parametrize("path", ["default", "generic", "fused"])
+@pytest.mark.parametrize("path", ["default", "generic", "fused", "legacy_mma"])
 @pytest.mark.parametrize("name", CASES)
 def test_reference_fixture(name, path):
     g, kw, batches = load_case(name)
-    if path != "default" and batches[0].shape[1] != 64:
-        pytest.skip("only d = 64 has more than one kernel path")
+    d = batches[0].shape[1]
+    if path != "default" and d != 64 and not (path == "legacy_mma" and d == 256):
+        pytest.skip("only d = 64 (and d = 256 for the Gram kernel) has more than one kernel path")
     det = OutlierMahalanobisB200(**kw)
     det.set_option(_cabi.SB_OPT_FORCE_GENERIC, int(path == "generic"))
     det.set_option(_cabi.SB_OPT_FUSED_PASS2, int(path == "fused"))
+    det.set_option(_cabi.SB_OPT_LEGACY_MMA, int(path == "legacy_mma"))
     k = min(kw.get("n_components", 3), batches[0].shape[1])
     n = 0
     strict_rows = 0
@@ -118,12 +120,14 @@ def test_c2_shape_primed_then_scored(gram_terms, fused):
         assert abs(a["value"] - b["value"]) <= 1e-4 * max(abs(b["value"]), 1e-9), a["key"]
 
 
+@pytest.mark.parametrize("legacy", [0, 1])
 @pytest.mark.parametrize("d", [128, 256])
-def test_wide_feature_tensor_paths(d):
+def test_wide_feature_tensor_paths(d, legacy):
     """d = 128 / 256 (config 5 width): blocked Gram kernel + generalised projection kernel vs the fp64 oracle."""
     prime, _ = synth.maha_rows_numpy(6000, d, 16, seed=51)
     X, labels = synth.maha_rows_numpy(30001, d, 16, seed=52)
     det, ref = OutlierMahalanobisB200(n_components=16), MahalanobisLean(n_components=16)
+    det.set_option(_cabi.SB_OPT_LEGACY_MMA, legacy)
     det.predict(prime, None), ref.predict(prime.astype(np.float64), None)
     pg, pr = det.predict(X, None), ref.predict(X.astype(np.float64), None)
     assert rel_err(det.score, ref.score).max() < TOL
