@@ -3,7 +3,8 @@
 // Replaces CoreMahalanobis.py:98-100 of the reference (the (nb,p,p) outer-product tensor and its sum) for
 // d = 64, 128 and 256: per sub-segment  s = sum(xc - a),  G = sum (xc - a)(xc - a)^T  (see maha_stats.cu).
 //
-// Data flow per CTA (one per SM, persistent over sub-segments), 128 threads:
+// Data flow per CTA (one per SM, persistent over sub-segments), 512 threads (the split/convert work is instruction
+// bound, 16 warps keep it ahead of the tensor pipe):
 //   global --LDG.128 (128 contiguous bytes per row and warp instruction)--> registers: clip, subtract the start-of-call
 //   mean, split every value into a TF32 "hi" part and the TF32-rounded remainder "lo"  --STS.128--> two shared-memory
 //   tiles T_hi, T_lo of 32 rows x D features in the canonical MN-major tf32 layout (SWIZZLE_128B_BASE32B: 128-byte
@@ -70,23 +71,28 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 }
 
 constexpr int kUmmaStages = 3;
-constexpr int kChunkRows = 32;
+// rows per chunk: 8192 / D, so every tile is 32 KB and every thread converts four float4 per chunk
+__host__ __device__ constexpr int umma_chunk_rows(int D) { return 8192 / D; }
 
 __host__ __device__ constexpr size_t umma_smem_bytes(int D, int terms) {
-  return (size_t)kUmmaStages * (terms == 3 ? 2 : 1) * kChunkRows * D * 4 + (size_t)3 * D * 4 + 1024 /* alignment slack */;
+  return (size_t)kUmmaStages * (terms == 3 ? 2 : 1) * umma_chunk_rows(D) * D * 4 + (size_t)3 * D * 4 + 1024 /* alignment slack */;
 }
 
+constexpr int kUmmaThreads = 512;
+
 template <int D, bool CLIP, int TERMS>
-__global__ void __launch_bounds__(128, 1)
+__global__ void __launch_bounds__(kUmmaThreads, 1)
 pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const float* __restrict__ mean_f,
                 const float* __restrict__ lo_f, const float* __restrict__ hi_f, float* __restrict__ partials) {
   constexpr int PS = D + D * D;
   constexpr int NSLAB = D / 32;                 // 128-byte feature slabs per row
   constexpr uint32_t LBO = 512;                 // between feature slabs of one 4-row atom
   constexpr uint32_t SBO = NSLAB * 512;         // between 4-row groups
-  constexpr int TILE = kChunkRows * D * 4;      // bytes of one 32 x D tile
+  constexpr int kChunkRows = umma_chunk_rows(D);
+  constexpr int NROW = kChunkRows / 32;         // rows per thread and chunk: (tid >> 4) + 32*j
+  constexpr int TILE = kChunkRows * D * 4;      // bytes of one tile (32 KB)
   constexpr int NT = TERMS == 3 ? 2 : 1;        // tiles per stage (hi, lo)
-  constexpr int NPIECE = D / 32;                // float4 pieces per thread and row set: lane&7 + 8*i
+  constexpr int NPIECE = D / 64;                // float4 pieces per thread: (tid & 15) + 16*i of row tid >> 4
   constexpr int TMEM_COLS = D == 256 ? 512 : D; // power of two >= columns used (D = 256 uses 384)
   extern __shared__ uint8_t umma_smem_raw[];
   uint8_t* tiles = (uint8_t*)(((uintptr_t)umma_smem_raw + 1023) & ~(uintptr_t)1023);
@@ -99,7 +105,7 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   __shared__ float ssum_s[D];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int rsub = lane >> 3, piece0 = lane & 7;  // 4 rows x 8 pieces (128 contiguous bytes of a row) per warp instruction
+  const int krow = tid >> 4, piece0 = tid & 15;  // a warp instruction reads 256 contiguous bytes of each of 2 rows
   for (int f = tid; f < D; f += blockDim.x) {
     ms[f] = mean_f[f];
     los[f] = CLIP ? lo_f[f] : 0.f;
@@ -126,22 +132,20 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   for (int sub = blockIdx.x; sub < lay.nsub; sub += gridDim.x) {
     const int64_t r0 = sub_begin(lay, sub), r1 = sub_begin(lay, sub + 1);
     const int nchunks = (int)((r1 - r0 + kChunkRows - 1) / kChunkRows);
-    float4 sums[2][NPIECE];
+    float4 sums[NPIECE];
 #pragma unroll
-    for (int h = 0; h < 2; ++h)
-#pragma unroll
-      for (int i = 0; i < NPIECE; ++i) sums[h][i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = 0; i < NPIECE; ++i) sums[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 
-    // rows of a chunk handled by this thread: 8*warp + rsub and 8*warp + 4 + rsub
-    float4 cur[2][NPIECE];
-    auto load_chunk = [&](int c, float4 (&v)[2][NPIECE]) {
+    // this thread's rows of a chunk: krow + 32*j; its float4 pieces: piece0 + 16*i
+    float4 cur[NROW][NPIECE];
+    auto load_chunk = [&](int c, float4 (&v)[NROW][NPIECE]) {
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int64_t row = r0 + (int64_t)c * kChunkRows + 8 * warp + 4 * h + rsub;
+      for (int j = 0; j < NROW; ++j) {
+        const int64_t row = r0 + (int64_t)c * kChunkRows + krow + 32 * j;
         const bool valid = row < r1;
         const float4* p = reinterpret_cast<const float4*>(X + row * ld);
 #pragma unroll
-        for (int i = 0; i < NPIECE; ++i) v[h][i] = valid ? ldg_stream_f4(p + piece0 + 8 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = 0; i < NPIECE; ++i) v[j][i] = valid ? ldg_stream_f4(p + piece0 + 16 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
     };
     if (nchunks > 0) load_chunk(0, cur);
@@ -149,17 +153,17 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
       const uint32_t stage = it % kUmmaStages;
       uint8_t* th = tiles + (size_t)stage * NT * TILE;  // hi tile; lo tile follows
       if (it >= (uint32_t)kUmmaStages) mbar_wait(smem_u32(&bar_empty[stage]), ((it / kUmmaStages) - 1) & 1);
-      float4 nxt[2][NPIECE];
+      float4 nxt[NROW][NPIECE];
       if (c + 1 < nchunks) load_chunk(c + 1, nxt);
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int k = 8 * warp + 4 * h + rsub;  // row inside the chunk
+      for (int j = 0; j < NROW; ++j) {
+        const int k = krow + 32 * j;  // row inside the chunk
         const bool valid = r0 + (int64_t)c * kChunkRows + k < r1;
 #pragma unroll
         for (int i = 0; i < NPIECE; ++i) {
-          const int piece = piece0 + 8 * i;      // float4 index inside the row: features 4*piece .. 4*piece+3
+          const int piece = piece0 + 16 * i;     // float4 index inside the row: features 4*piece .. 4*piece+3
           const float4 m4 = *reinterpret_cast<const float4*>(ms + 4 * piece);
-          float v[4] = {cur[h][i].x, cur[h][i].y, cur[h][i].z, cur[h][i].w};
+          float v[4] = {cur[j][i].x, cur[j][i].y, cur[j][i].z, cur[j][i].w};
           const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
           if (CLIP) {
             const float4 l4 = *reinterpret_cast<const float4*>(los + 4 * piece);
@@ -176,7 +180,7 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
             if (TERMS == 3) lo4[e] = to_tf32(dv - __uint_as_float(hi4[e]));
             v[e] = dv;
           }
-          sums[h][i].x += v[0]; sums[h][i].y += v[1]; sums[h][i].z += v[2]; sums[h][i].w += v[3];
+          sums[i].x += v[0]; sums[i].y += v[1]; sums[i].z += v[2]; sums[i].w += v[3];
           // canonical address of (row k, features 4*piece..): slab = piece >> 3, byte in the 128-byte row b = 16*(piece&7)
           const uint32_t b = 16u * (piece & 7);
           const uint32_t off = (uint32_t)(k >> 2) * SBO + (uint32_t)(piece >> 3) * LBO + (uint32_t)(k & 3) * 128u +
@@ -225,9 +229,9 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
       }
       if (c + 1 < nchunks) {
 #pragma unroll
-        for (int h = 0; h < 2; ++h)
+        for (int j = 0; j < NROW; ++j)
 #pragma unroll
-          for (int i = 0; i < NPIECE; ++i) cur[h][i] = nxt[h][i];
+          for (int i = 0; i < NPIECE; ++i) cur[j][i] = nxt[j][i];
       }
     }
 
@@ -237,18 +241,14 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < NPIECE; ++i) {
-      float4 a = sums[0][i];
-      a.x += sums[1][i].x; a.y += sums[1][i].y; a.z += sums[1][i].z; a.w += sums[1][i].w;
-      // lanes with the same piece0 hold different rows: reduce over rsub (lane bits 3,4)
-#pragma unroll
-      for (int o = 8; o <= 16; o <<= 1) {
-        a.x += __shfl_xor_sync(0xffffffffu, a.x, o);
-        a.y += __shfl_xor_sync(0xffffffffu, a.y, o);
-        a.z += __shfl_xor_sync(0xffffffffu, a.z, o);
-        a.w += __shfl_xor_sync(0xffffffffu, a.w, o);
-      }
-      if (rsub == 0) {
-        const int f = 4 * (piece0 + 8 * i);
+      float4 a = sums[i];
+      // the two half-warps hold two different rows of the same pieces
+      a.x += __shfl_xor_sync(0xffffffffu, a.x, 16);
+      a.y += __shfl_xor_sync(0xffffffffu, a.y, 16);
+      a.z += __shfl_xor_sync(0xffffffffu, a.z, 16);
+      a.w += __shfl_xor_sync(0xffffffffu, a.w, 16);
+      if (lane < 16) {
+        const int f = 4 * (piece0 + 16 * i);
         atomicAdd(&ssum_s[f], a.x); atomicAdd(&ssum_s[f + 1], a.y); atomicAdd(&ssum_s[f + 2], a.z); atomicAdd(&ssum_s[f + 3], a.w);
       }
     }
@@ -261,13 +261,14 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
       acc_parity ^= 1u;
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       uint32_t r[32];
+      const int quarter = warp & 3, cblk = warp >> 2;  // TMEM lanes 32*quarter.., and which columns this warp drains
       if (D == 64) {
-        // M = 64: accumulator row m sits in TMEM lane (m & 15) + 32 * (m >> 4): lanes 0-15 of every warp's quarter
-#pragma unroll
-        for (int c0 = 0; c0 < 64; c0 += 32) {
-          tmem_ld32(tmem + ((uint32_t)(32 * warp) << 16) + c0, r);
+        // M = 64: accumulator row m sits in TMEM lane (m & 15) + 32 * (m >> 4): lanes 0-15 of every quarter
+        if (cblk < 2) {
+          const int c0 = 32 * cblk;
+          tmem_ld32(tmem + ((uint32_t)(32 * quarter) << 16) + c0, r);
           if (lane < 16) {
-            float4* dst = reinterpret_cast<float4*>(G + (size_t)(16 * warp + lane) * D + c0);
+            float4* dst = reinterpret_cast<float4*>(G + (size_t)(16 * quarter + lane) * D + c0);
 #pragma unroll
             for (int q = 0; q < 8; ++q)
               dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]), __uint_as_float(r[4 * q + 2]),
@@ -275,11 +276,11 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
           }
         }
       } else {
-        const int m = 32 * warp + lane;  // M = 128: row m in lane m
+        const int m = 32 * quarter + lane;  // M = 128: row m in lane m
         constexpr int NC0 = D == 256 ? 256 : D;
 #pragma unroll 1
-        for (int c0 = 0; c0 < NC0; c0 += 32) {
-          tmem_ld32(tmem + ((uint32_t)(32 * warp) << 16) + c0, r);
+        for (int c0 = 32 * cblk; c0 < NC0; c0 += 128) {
+          tmem_ld32(tmem + ((uint32_t)(32 * quarter) << 16) + c0, r);
           float4* dst = reinterpret_cast<float4*>(G + (size_t)m * D + c0);
 #pragma unroll
           for (int q = 0; q < 8; ++q)
@@ -291,15 +292,13 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
           }
         }
         if (D == 256) {
-#pragma unroll 1
-          for (int c0 = 0; c0 < 128; c0 += 32) {
-            tmem_ld32(tmem + ((uint32_t)(32 * warp) << 16) + 256 + c0, r);
-            float4* dst = reinterpret_cast<float4*>(G + (size_t)(128 + m) * D + 128 + c0);
+          const int c0 = 32 * cblk;  // 128 columns of the second accumulator: one block per warp
+          tmem_ld32(tmem + ((uint32_t)(32 * quarter) << 16) + 256 + c0, r);
+          float4* dst = reinterpret_cast<float4*>(G + (size_t)(128 + m) * D + 128 + c0);
 #pragma unroll
-            for (int q = 0; q < 8; ++q)
-              dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]), __uint_as_float(r[4 * q + 2]),
-                                   __uint_as_float(r[4 * q + 3]));
-          }
+          for (int q = 0; q < 8; ++q)
+            dst[q] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]), __uint_as_float(r[4 * q + 2]),
+                                 __uint_as_float(r[4 * q + 3]));
         }
       }
     } else {
@@ -323,7 +322,7 @@ int launch_umma_d(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws
   do {                                                                                                                  \
     const size_t smem = umma_smem_bytes(D, TERMSV);                                                                     \
     SB_CUDA(cudaFuncSetAttribute(pass1_gram_umma<D, CLIPV, TERMSV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    pass1_gram_umma<D, CLIPV, TERMSV><<<grid, 128, smem, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials); \
+    pass1_gram_umma<D, CLIPV, TERMSV><<<grid, kUmmaThreads, smem, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials); \
   } while (0)
   if (h->use_clip) {
     if (h->gram_terms == 3) SB_UMMA_LAUNCH(true, 3); else SB_UMMA_LAUNCH(true, 1);
