@@ -78,10 +78,11 @@ __host__ __device__ constexpr size_t umma_smem_bytes(int D, int terms) {
   return (size_t)kUmmaStages * (terms == 3 ? 2 : 1) * umma_chunk_rows(D) * D * 4 + (size_t)3 * D * 4 + 1024 /* alignment slack */;
 }
 
-constexpr int kUmmaThreads = 512;
+constexpr int kUmmaThreads = 512;            // producer threads (16 warps); one more warp issues the MMAs
+constexpr int kUmmaBlock = kUmmaThreads + 32;
 
 template <int D, bool CLIP, int TERMS>
-__global__ void __launch_bounds__(kUmmaThreads, 1)
+__global__ void __launch_bounds__(kUmmaBlock, 1)
 pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const float* __restrict__ mean_f,
                 const float* __restrict__ lo_f, const float* __restrict__ hi_f, float* __restrict__ partials) {
   constexpr int PS = D + D * D;
@@ -99,22 +100,27 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   float* ms = reinterpret_cast<float*>(tiles + kUmmaStages * NT * TILE);
   float* los = ms + D;
   float* his = los + D;
-  __shared__ uint64_t bar_empty[kUmmaStages];
-  __shared__ uint64_t bar_acc;
+  __shared__ uint64_t bar_full[kUmmaStages];   // 16 producer warps have filled the slot
+  __shared__ uint64_t bar_empty[kUmmaStages];  // the MMAs reading the slot have completed (tcgen05.commit)
+  __shared__ uint64_t bar_acc;                 // all MMAs of the sub-segment have completed
+  __shared__ uint64_t bar_tfree;               // 16 producer warps have drained the accumulator
   __shared__ uint32_t tmem_base_s;
   __shared__ float ssum_s[D];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int krow = tid >> 4, piece0 = tid & 15;  // a warp instruction reads 256 contiguous bytes of each of 2 rows
-  for (int f = tid; f < D; f += blockDim.x) {
+  for (int f = tid; f < D; f += kUmmaBlock) {
     ms[f] = mean_f[f];
     los[f] = CLIP ? lo_f[f] : 0.f;
     his[f] = CLIP ? hi_f[f] : 0.f;
   }
   if (tid == 0) {
-    for (int s = 0; s < kUmmaStages; ++s)
+    for (int s = 0; s < kUmmaStages; ++s) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 16;" ::"r"(smem_u32(&bar_full[s])));
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar_empty[s])));
+    }
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar_acc)));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 16;" ::"r"(smem_u32(&bar_tfree)));
     asm volatile("fence.mbarrier_init.release.cluster;");
   }
   if (warp == 0) {
@@ -127,6 +133,64 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   const uint32_t tmem = tmem_base_s;
   const uint32_t tiles_u32 = smem_u32(tiles);
 
+  if (warp == kUmmaThreads / 32) {
+    // ===== MMA warp: one lane issues; walks the same (sub-segment, chunk) sequence as the producers
+    if (lane == 0) {
+      uint32_t itm = 0, tfree_parity = 0;
+      bool first_sub = true;
+      for (int sub = blockIdx.x; sub < lay.nsub; sub += gridDim.x) {
+        const int64_t r0 = sub_begin(lay, sub), r1 = sub_begin(lay, sub + 1);
+        const int nchunks = (int)((r1 - r0 + kChunkRows - 1) / kChunkRows);
+        if (nchunks == 0) continue;
+        if (!first_sub) {  // the previous accumulator must have been read out
+          mbar_wait(smem_u32(&bar_tfree), tfree_parity);
+          tfree_parity ^= 1u;
+        }
+        first_sub = false;
+        for (int c = 0; c < nchunks; ++c, ++itm) {
+          const uint32_t stage = itm % kUmmaStages;
+          mbar_wait(smem_u32(&bar_full[stage]), (itm / kUmmaStages) & 1);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t hbase = tiles_u32 + stage * NT * TILE, lbase = hbase + TILE;
+          constexpr uint64_t kstep = (uint64_t)((2u * SBO) >> 4);  // 8 rows = two 4-row groups, in descriptor units
+          if (D <= 128) {
+            constexpr uint32_t idesc = umma_idesc(D, D);
+            uint64_t dh = umma_desc(hbase, LBO, SBO), dl = umma_desc(lbase, LBO, SBO);
+#pragma unroll 4
+            for (int ks = 0; ks < kChunkRows / 8; ++ks, dh += kstep, dl += kstep) {
+              umma_tf32(tmem, dh, dh, idesc, (c > 0 || ks > 0) ? 1u : 0u);
+              if (TERMS == 3) {
+                umma_tf32(tmem, dh, dl, idesc, 1u);
+                umma_tf32(tmem, dl, dh, idesc, 1u);
+              }
+            }
+          } else {
+            // rows 0-127 against all 256 columns -> TMEM columns [0,256); rows 128-255 against columns 128-255 -> [256,384)
+            constexpr uint32_t id0 = umma_idesc(128, 256), id1 = umma_idesc(128, 128);
+            uint64_t dh0 = umma_desc(hbase, LBO, SBO), dl0 = umma_desc(lbase, LBO, SBO);
+            uint64_t dh1 = umma_desc(hbase + 4 * LBO, LBO, SBO), dl1 = umma_desc(lbase + 4 * LBO, LBO, SBO);
+#pragma unroll
+            for (int ks = 0; ks < kChunkRows / 8; ++ks, dh0 += kstep, dl0 += kstep, dh1 += kstep, dl1 += kstep) {
+              const uint32_t acc = (c > 0 || ks > 0) ? 1u : 0u;
+              umma_tf32(tmem, dh0, dh0, id0, acc);
+              umma_tf32(tmem + 256, dh1, dh1, id1, acc);
+              if (TERMS == 3) {
+                umma_tf32(tmem, dh0, dl0, id0, 1u);
+                umma_tf32(tmem, dl0, dh0, id0, 1u);
+                umma_tf32(tmem + 256, dh1, dl1, id1, 1u);
+                umma_tf32(tmem + 256, dl1, dh1, id1, 1u);
+              }
+            }
+          }
+          // the ring slot is free again once these MMAs have read it
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar_empty[stage])) : "memory");
+          if (c == nchunks - 1)
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar_acc)) : "memory");
+        }
+      }
+    }
+  } else {
+  // ===== producer warps (16): load, clip, shift, split, store tiles; epilogue at the end of each sub-segment
   uint32_t it = 0;        // chunks issued so far by this CTA (ring position)
   uint32_t acc_parity = 0;
   for (int sub = blockIdx.x; sub < lay.nsub; sub += gridDim.x) {
@@ -190,43 +254,8 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
         }
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the tensor core
-      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-      __syncthreads();
-      if (tid == 0) {
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t hbase = tiles_u32 + stage * NT * TILE, lbase = hbase + TILE;
-#pragma unroll
-        for (int ks = 0; ks < kChunkRows / 8; ++ks) {
-          const uint32_t koff = (uint32_t)ks * 2u * SBO;  // 8 rows = two 4-row groups
-          const uint32_t first = (c > 0 || ks > 0) ? 1u : 0u;
-          if (D <= 128) {
-            constexpr uint32_t idesc = umma_idesc(D, D);
-            const uint64_t dh = umma_desc(hbase + koff, LBO, SBO), dl = umma_desc(lbase + koff, LBO, SBO);
-            umma_tf32(tmem, dh, dh, idesc, first);
-            if (TERMS == 3) {
-              umma_tf32(tmem, dh, dl, idesc, 1u);
-              umma_tf32(tmem, dl, dh, idesc, 1u);
-            }
-          } else {
-            // rows 0-127 against all 256 columns -> TMEM columns [0,256); rows 128-255 against columns 128-255 -> [256,384)
-            constexpr uint32_t id0 = umma_idesc(128, 256), id1 = umma_idesc(128, 128);
-            const uint64_t dh0 = umma_desc(hbase + koff, LBO, SBO), dl0 = umma_desc(lbase + koff, LBO, SBO);
-            const uint64_t dh1 = umma_desc(hbase + koff + 4 * LBO, LBO, SBO), dl1 = umma_desc(lbase + koff + 4 * LBO, LBO, SBO);
-            umma_tf32(tmem, dh0, dh0, id0, first);
-            umma_tf32(tmem + 256, dh1, dh1, id1, first);
-            if (TERMS == 3) {
-              umma_tf32(tmem, dh0, dl0, id0, 1u);
-              umma_tf32(tmem, dl0, dh0, id0, 1u);
-              umma_tf32(tmem + 256, dh1, dl1, id1, 1u);
-              umma_tf32(tmem + 256, dl1, dh1, id1, 1u);
-            }
-          }
-        }
-        // the ring slot is free again once these MMAs have read it
-        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar_empty[stage])) : "memory");
-        if (c == nchunks - 1)
-          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar_acc)) : "memory");
-      }
+      __syncwarp();
+      if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&bar_full[stage])) : "memory");
       if (c + 1 < nchunks) {
 #pragma unroll
         for (int j = 0; j < NROW; ++j)
@@ -237,8 +266,8 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
 
     // ---- end of the sub-segment: row sums, then the accumulator
     float* part = partials + (size_t)sub * PS;
-    for (int f = tid; f < D; f += blockDim.x) ssum_s[f] = 0.f;
-    __syncthreads();
+    for (int f = tid; f < D; f += kUmmaThreads) ssum_s[f] = 0.f;
+    asm volatile("bar.sync 1, %0;" ::"n"(kUmmaThreads) : "memory");
 #pragma unroll
     for (int i = 0; i < NPIECE; ++i) {
       float4 a = sums[i];
@@ -252,8 +281,8 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
         atomicAdd(&ssum_s[f], a.x); atomicAdd(&ssum_s[f + 1], a.y); atomicAdd(&ssum_s[f + 2], a.z); atomicAdd(&ssum_s[f + 3], a.w);
       }
     }
-    __syncthreads();
-    for (int f = tid; f < D; f += blockDim.x) part[f] = ssum_s[f];
+    asm volatile("bar.sync 1, %0;" ::"n"(kUmmaThreads) : "memory");
+    for (int f = tid; f < D; f += kUmmaThreads) part[f] = ssum_s[f];
 
     float* G = part + D;
     if (nchunks > 0) {
@@ -302,12 +331,18 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
         }
       }
     } else {
-      for (int e = tid; e < D * D; e += blockDim.x) G[e] = 0.f;
+      for (int e = tid; e < D * D; e += kUmmaThreads) G[e] = 0.f;
     }
-    // every warp has drained its lanes before the next sub-segment's first MMA overwrites the accumulator
+    // tell the MMA warp that this warp has drained its part of the accumulator; keep the producers together so that
+    // ssum_s is not reused early
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
+    __syncwarp();
+    if (nchunks > 0 && lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&bar_tfree)) : "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(kUmmaThreads) : "memory");
   }
+  }  // producer role
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
   if (warp == 0) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TMEM_COLS));
@@ -322,7 +357,7 @@ int launch_umma_d(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws
   do {                                                                                                                  \
     const size_t smem = umma_smem_bytes(D, TERMSV);                                                                     \
     SB_CUDA(cudaFuncSetAttribute(pass1_gram_umma<D, CLIPV, TERMSV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    pass1_gram_umma<D, CLIPV, TERMSV><<<grid, kUmmaThreads, smem, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials); \
+    pass1_gram_umma<D, CLIPV, TERMSV><<<grid, kUmmaBlock, smem, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials); \
   } while (0)
   if (h->use_clip) {
     if (h->gram_terms == 3) SB_UMMA_LAUNCH(true, 3); else SB_UMMA_LAUNCH(true, 1);
