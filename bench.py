@@ -283,10 +283,10 @@ def main():
         pass2_ms = kern_ms[3] + kern_ms[4]
         # the dominant kernel of the step: pass-1 Gram statistics or pass 2 (projection + chain, one algorithmic unit)
         if kern_ms[0] >= pass2_ms:
-            dom = {"kernel": "pass1_gram64_tf32 (clip, row sums, 3xTF32 Gram on mma.sync)", "ms": kern_ms[0],
-                   "bytes": pass1_bytes, "traffic_key": "pass1_gram64_dram_bytes_per_launch"}
+            dom = {"kernel": "pass1_gram_umma<64> (clip, row sums, 3xTF32 Gram on tcgen05.mma kind::tf32)", "ms": kern_ms[0],
+                   "bytes": pass1_bytes, "traffic_key": "pass1_dram_bytes_per_launch"}
         else:
-            dom = {"kernel": "pass 2 = project64 + chain16 (project, inverse chain, score, flag)", "ms": pass2_ms,
+            dom = {"kernel": "pass 2 = project_rows<2,clip> + chain16<clip> (project on mma.sync 3xTF32, inverse chain, score, flag)", "ms": pass2_ms,
                    "bytes": chain_bytes, "traffic_key": "pass2_dram_bytes_per_launch"}
         traffic = None
         if os.path.isfile(tpath):

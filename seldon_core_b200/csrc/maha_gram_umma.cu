@@ -3,21 +3,27 @@
 // Replaces CoreMahalanobis.py:98-100 of the reference (the (nb,p,p) outer-product tensor and its sum) for
 // d = 64, 128 and 256: per sub-segment  s = sum(xc - a),  G = sum (xc - a)(xc - a)^T  (see maha_stats.cu).
 //
-// Data flow per CTA (one per SM, persistent over sub-segments), 512 threads (the split/convert work is instruction
-// bound, 16 warps keep it ahead of the tensor pipe):
-//   global --LDG.128 (128 contiguous bytes per row and warp instruction)--> registers: clip, subtract the start-of-call
-//   mean, split every value into a TF32 "hi" part and the TF32-rounded remainder "lo"  --STS.128--> two shared-memory
-//   tiles T_hi, T_lo of 32 rows x D features in the canonical MN-major tf32 layout (SWIZZLE_128B_BASE32B: 128-byte
-//   feature slabs, 4-row atoms, 32-byte chunks XOR-ed with row & 3; verified on hardware with tools/umma_probe.cu)
-//   --tcgen05.mma.kind::tf32, A = B = the same tile (the Gram is T^T T)--> fp32 accumulator in TMEM
-//   (3 MMAs per 8 rows: hi*hi + hi*lo + lo*hi = the 3xTF32 product with fp32-level accuracy).
-// A ring of 3 tile pairs lets the loads/splits of chunk c+1.. overlap the MMAs of chunk c; tcgen05.commit releases a
-// ring slot through an mbarrier.  At the end of a sub-segment the accumulator is read back with tcgen05.ld and stored
-// as the sub-segment's partial.  d = 256 uses two accumulators (rows 0-127 x 256 columns, rows 128-255 x columns
-// 128-255: the block below the diagonal is mirrored on store), 384 of the 512 TMEM columns.
+// Data flow per CTA (one per SM, persistent over sub-segments): 16 producer warps + 1 MMA warp.
+//   producers: global --LDG.128 (a warp instruction reads 256 contiguous bytes of each of two rows; one or two 32 KB
+//   chunks per SM stay in flight ahead of the chunk being converted)--> registers: clip, subtract the start-of-call mean,
+//   split every value into a TF32 "hi" part and the TF32-rounded remainder "lo" (integer round-to-nearest, 2 instructions)
+//   --STS.128--> shared-memory tiles in the canonical MN-major tf32 layout (SWIZZLE_128B_BASE32B: 128-byte feature slabs,
+//   4-row atoms, 32-byte chunks XOR-ed with row & 3; verified on hardware with tools/umma_probe.cu); fence.proxy.async,
+//   one mbarrier arrive per warp on the slot's "full" barrier.
+//   MMA warp (one lane): waits "full", issues tcgen05.mma.kind::tf32 with A = B = descriptors of the same tile (the Gram
+//   is T^T T), fp32 accumulator in TMEM; tcgen05.commit releases the slot ("empty") and, after the last chunk of a
+//   sub-segment, signals the producers to drain the accumulator with tcgen05.ld and store the sub-segment's partial.
+//   3xTF32 accuracy: hi*hi + hi*lo + lo*hi.
+//     d = 64:  lo is stored as two more feature slabs of the hi tile, ONE M = 128, N = 64 MMA per 8 rows gives
+//              [hi^T hi; lo^T hi] and the epilogue forms G = HH + LH + LH^T (a third of the tensor work and half of the
+//              shared-memory reads of three M = 64 MMAs, which also run the pipe at half rate);
+//     d = 128: three M = N = 128 MMAs per 8 rows;
+//     d = 256: two accumulators (rows 0-127 x 256 columns, rows 128-255 x columns 128-255: the block below the
+//              diagonal is mirrored on store), 384 of the 512 TMEM columns, six MMAs per 8 rows.
 //
-// Bounds: d = 64: the tiles are read twice per MMA (A and B) so shared-memory bandwidth, not HBM, is the limiter at
-// roughly 0.7 of the HBM rate; d = 256: tensor pipe (2*d*d*0.75*3 flop per row).
+// Bounds (B200, measured, 16Mi rows): d = 64: 1.07 ms = 4.0 TB/s, 61 % of the measured HBM copy rate; the producers'
+// issue rate (about 270 instructions per thread and 128-row chunk) is the limiter.  d = 128: 2.7 TB/s, tensor pipe and
+// HBM about level.  d = 256: 2.1 TB/s, tensor pipe (2*d*d*0.75*3 flop per row).
 #include "maha.cuh"
 
 namespace sb {
@@ -29,6 +35,14 @@ __device__ __forceinline__ uint32_t to_tf32(float x) {
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
   return r;
+}
+
+// round to nearest (ties away from zero) to the 10-bit TF32 mantissa with integer arithmetic: what cvt.rna.tf32.f32
+// computes for finite inputs, in two instructions (ptxas expands the cvt into about six on sm_100a)
+__device__ __forceinline__ uint32_t round_tf32(float x) { return (__float_as_uint(x) + 0x1000u) & 0xffffe000u; }
+
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
@@ -88,13 +102,22 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   constexpr int PS = D + D * D;
   constexpr int NSLAB = D / 32;                 // 128-byte feature slabs per row
   constexpr uint32_t LBO = 512;                 // between feature slabs of one 4-row atom
-  constexpr uint32_t SBO = NSLAB * 512;         // between 4-row groups
+  // Symmetry: hi*lo and lo*hi are transposes of each other, so only  HH = sum hi^T hi  and  LH = sum lo^T hi  are
+  // contracted and the epilogue forms  G = HH + LH + LH^T.
+  //   d = 64  (STACK): lo is stored as two more feature slabs of the hi tile; ONE M = 128, N = 64 MMA per 8 rows gives
+  //                    [HH; LH] in TMEM lanes 0-63 / 64-127 (M = 128 also runs the tensor pipe at full rate, M = 64 at half)
+  // (d = 128 with two accumulators HH, LH was measured slower than the plain three products: the longer epilogue is not
+  // hidden behind the MMAs of a 900-row sub-segment.)
+  constexpr bool STACK = D == 64 && TERMS == 3;
+  constexpr bool PF2 = D == 64;  // prefetch distance 2 (d = 64 is HBM-latency bound; the wider shapes are tensor bound)
+  constexpr uint32_t SBO = (STACK ? 2 : 1) * NSLAB * 512;  // between 4-row groups
   constexpr int kChunkRows = umma_chunk_rows(D);
   constexpr int NROW = kChunkRows / 32;         // rows per thread and chunk: (tid >> 4) + 32*j
   constexpr int TILE = kChunkRows * D * 4;      // bytes of one tile (32 KB)
   constexpr int NT = TERMS == 3 ? 2 : 1;        // tiles per stage (hi, lo)
   constexpr int NPIECE = D / 64;                // float4 pieces per thread: (tid & 15) + 16*i of row tid >> 4
-  constexpr int TMEM_COLS = D == 256 ? 512 : D; // power of two >= columns used (D = 256 uses 384)
+  constexpr uint32_t LO_OFF = STACK ? NSLAB * LBO : TILE;  // from a hi element to its lo element
+  constexpr int TMEM_COLS = D == 256 ? 512 : D;  // power of two >= columns used (D = 256 uses 384)
   extern __shared__ uint8_t umma_smem_raw[];
   uint8_t* tiles = (uint8_t*)(((uintptr_t)umma_smem_raw + 1023) & ~(uintptr_t)1023);
   float* ms = reinterpret_cast<float*>(tiles + kUmmaStages * NT * TILE);
@@ -153,7 +176,12 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t hbase = tiles_u32 + stage * NT * TILE, lbase = hbase + TILE;
           constexpr uint64_t kstep = (uint64_t)((2u * SBO) >> 4);  // 8 rows = two 4-row groups, in descriptor units
-          if (D <= 128) {
+          if (STACK) {
+            constexpr uint32_t idesc = umma_idesc(128, 64);
+            uint64_t dh = umma_desc(hbase, LBO, SBO);
+#pragma unroll 4
+            for (int ks = 0; ks < kChunkRows / 8; ++ks, dh += kstep) umma_tf32(tmem, dh, dh, idesc, (c > 0 || ks > 0) ? 1u : 0u);
+          } else if (D <= 128) {
             constexpr uint32_t idesc = umma_idesc(D, D);
             uint64_t dh = umma_desc(hbase, LBO, SBO), dl = umma_desc(lbase, LBO, SBO);
 #pragma unroll 4
@@ -192,6 +220,21 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   } else {
   // ===== producer warps (16): load, clip, shift, split, store tiles; epilogue at the end of each sub-segment
   uint32_t it = 0;        // chunks issued so far by this CTA (ring position)
+  // byte offset of (row krow, piece piece0) in a tile: slab = piece >> 3, 16-byte column (piece & 7) of the 128-byte row,
+  // 32-byte chunks XOR-ed with row & 3
+  const uint32_t b0 = 16u * (piece0 & 7);
+  const uint32_t off0 = (uint32_t)(krow >> 2) * SBO + (uint32_t)(piece0 >> 3) * LBO + (uint32_t)(krow & 3) * 128u +
+                        ((((b0 >> 5) ^ (uint32_t)(krow & 3)) << 5) | (b0 & 31u));
+  constexpr bool HOIST = NPIECE <= 2;  // keep this thread's mean / clip bounds in registers
+  float4 m_r[HOIST ? NPIECE : 1], l_r[HOIST ? NPIECE : 1], h_r[HOIST ? NPIECE : 1];
+  if (HOIST) {
+#pragma unroll
+    for (int i = 0; i < NPIECE; ++i) {
+      m_r[i] = *reinterpret_cast<const float4*>(ms + 4 * (piece0 + 16 * i));
+      l_r[i] = *reinterpret_cast<const float4*>(los + 4 * (piece0 + 16 * i));
+      h_r[i] = *reinterpret_cast<const float4*>(his + 4 * (piece0 + 16 * i));
+    }
+  }
   uint32_t acc_parity = 0;
   for (int sub = blockIdx.x; sub < lay.nsub; sub += gridDim.x) {
     const int64_t r0 = sub_begin(lay, sub), r1 = sub_begin(lay, sub + 1);
@@ -201,7 +244,6 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
     for (int i = 0; i < NPIECE; ++i) sums[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 
     // this thread's rows of a chunk: krow + 32*j; its float4 pieces: piece0 + 16*i
-    float4 cur[NROW][NPIECE];
     auto load_chunk = [&](int c, float4 (&v)[NROW][NPIECE]) {
 #pragma unroll
       for (int j = 0; j < NROW; ++j) {
@@ -212,55 +254,85 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
         for (int i = 0; i < NPIECE; ++i) v[j][i] = valid ? ldg_stream_f4(p + piece0 + 16 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
     };
-    if (nchunks > 0) load_chunk(0, cur);
-    for (int c = 0; c < nchunks; ++c, ++it) {
+    // clip, shift, split into hi/lo and store chunk c (held in v4) into its ring slot; then signal the MMA warp
+    auto convert_chunk = [&](int c, const float4 (&v4)[NROW][NPIECE]) {
       const uint32_t stage = it % kUmmaStages;
-      uint8_t* th = tiles + (size_t)stage * NT * TILE;  // hi tile; lo tile follows
+      const uint32_t th = tiles_u32 + stage * NT * TILE + off0;  // hi tile (+ this thread's offset); lo at + LO_OFF
       if (it >= (uint32_t)kUmmaStages) mbar_wait(smem_u32(&bar_empty[stage]), ((it / kUmmaStages) - 1) & 1);
-      float4 nxt[NROW][NPIECE];
-      if (c + 1 < nchunks) load_chunk(c + 1, nxt);
 #pragma unroll
       for (int j = 0; j < NROW; ++j) {
-        const int k = krow + 32 * j;  // row inside the chunk
-        const bool valid = r0 + (int64_t)c * kChunkRows + k < r1;
+        const bool valid = r0 + (int64_t)c * kChunkRows + krow + 32 * j < r1;
 #pragma unroll
         for (int i = 0; i < NPIECE; ++i) {
-          const int piece = piece0 + 16 * i;     // float4 index inside the row: features 4*piece .. 4*piece+3
-          const float4 m4 = *reinterpret_cast<const float4*>(ms + 4 * piece);
-          float v[4] = {cur[j][i].x, cur[j][i].y, cur[j][i].z, cur[j][i].w};
-          const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
-          if (CLIP) {
-            const float4 l4 = *reinterpret_cast<const float4*>(los + 4 * piece);
-            const float4 h4 = *reinterpret_cast<const float4*>(his + 4 * piece);
-            const float ll[4] = {l4.x, l4.y, l4.z, l4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) v[e] = fminf(fmaxf(v[e], ll[e]), hh[e]);
+          float v[4] = {v4[j][i].x, v4[j][i].y, v4[j][i].z, v4[j][i].w};
+          float mm[4], ll[4], hh[4];
+          if (HOIST) {
+            mm[0] = m_r[i].x; mm[1] = m_r[i].y; mm[2] = m_r[i].z; mm[3] = m_r[i].w;
+            if (CLIP) {
+              ll[0] = l_r[i].x; ll[1] = l_r[i].y; ll[2] = l_r[i].z; ll[3] = l_r[i].w;
+              hh[0] = h_r[i].x; hh[1] = h_r[i].y; hh[2] = h_r[i].z; hh[3] = h_r[i].w;
+            }
+          } else {
+            const int piece = piece0 + 16 * i;
+            const float4 m4 = *reinterpret_cast<const float4*>(ms + 4 * piece);
+            mm[0] = m4.x; mm[1] = m4.y; mm[2] = m4.z; mm[3] = m4.w;
+            if (CLIP) {
+              const float4 l4 = *reinterpret_cast<const float4*>(los + 4 * piece);
+              const float4 h4 = *reinterpret_cast<const float4*>(his + 4 * piece);
+              ll[0] = l4.x; ll[1] = l4.y; ll[2] = l4.z; ll[3] = l4.w;
+              hh[0] = h4.x; hh[1] = h4.y; hh[2] = h4.z; hh[3] = h4.w;
+            }
           }
           uint32_t hi4[4], lo4[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
+            if (CLIP) v[e] = fminf(fmaxf(v[e], ll[e]), hh[e]);
             const float dv = valid ? v[e] - mm[e] : 0.f;
-            hi4[e] = to_tf32(dv);
-            if (TERMS == 3) lo4[e] = to_tf32(dv - __uint_as_float(hi4[e]));
+            hi4[e] = round_tf32(dv);
+            if (TERMS == 3) lo4[e] = round_tf32(dv - __uint_as_float(hi4[e]));
             v[e] = dv;
           }
           sums[i].x += v[0]; sums[i].y += v[1]; sums[i].z += v[2]; sums[i].w += v[3];
-          // canonical address of (row k, features 4*piece..): slab = piece >> 3, byte in the 128-byte row b = 16*(piece&7)
-          const uint32_t b = 16u * (piece & 7);
-          const uint32_t off = (uint32_t)(k >> 2) * SBO + (uint32_t)(piece >> 3) * LBO + (uint32_t)(k & 3) * 128u +
-                               ((((b >> 5) ^ (uint32_t)(k & 3)) << 5) | (b & 31u));
-          *reinterpret_cast<uint4*>(th + off) = make_uint4(hi4[0], hi4[1], hi4[2], hi4[3]);
-          if (TERMS == 3) *reinterpret_cast<uint4*>(th + TILE + off) = make_uint4(lo4[0], lo4[1], lo4[2], lo4[3]);
+          // row k = krow + 32 j sits 8 j four-row groups after row krow; piece + 16 i sits 2 i slabs after piece
+          const uint32_t a = th + (uint32_t)(8 * j) * SBO + (uint32_t)(2 * i) * LBO;
+          sts128(a, hi4[0], hi4[1], hi4[2], hi4[3]);
+          if (TERMS == 3) sts128(a + LO_OFF, lo4[0], lo4[1], lo4[2], lo4[3]);
         }
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the tensor core
       __syncwarp();
       if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&bar_full[stage])) : "memory");
-      if (c + 1 < nchunks) {
-#pragma unroll
-        for (int j = 0; j < NROW; ++j)
-#pragma unroll
-          for (int i = 0; i < NPIECE; ++i) cur[j][i] = nxt[j][i];
+      ++it;
+    };
+
+    if (PF2) {
+      // two chunks (64 KB per SM) stay in flight ahead of the one being converted: one does not cover the HBM latency at
+      // full rate (148 SMs x 32 KB / ~1.5 us = 3 TB/s).  Three named buffers, rotated by unrolling (no register moves).
+      float4 bufA[NROW][NPIECE], bufB[NROW][NPIECE], bufC[NROW][NPIECE];
+      if (nchunks > 0) load_chunk(0, bufA);
+      if (nchunks > 1) load_chunk(1, bufB);
+      for (int c = 0; c < nchunks; c += 3) {
+        if (c + 2 < nchunks) load_chunk(c + 2, bufC);
+        convert_chunk(c, bufA);
+        if (c + 1 < nchunks) {
+          if (c + 3 < nchunks) load_chunk(c + 3, bufA);
+          convert_chunk(c + 1, bufB);
+        }
+        if (c + 2 < nchunks) {
+          if (c + 4 < nchunks) load_chunk(c + 4, bufB);
+          convert_chunk(c + 2, bufC);
+        }
+      }
+    } else {
+      float4 bufA[NROW][NPIECE], bufB[NROW][NPIECE];
+      if (nchunks > 0) load_chunk(0, bufA);
+      for (int c = 0; c < nchunks; c += 2) {
+        if (c + 1 < nchunks) load_chunk(c + 1, bufB);
+        convert_chunk(c, bufA);
+        if (c + 1 < nchunks) {
+          if (c + 2 < nchunks) load_chunk(c + 2, bufA);
+          convert_chunk(c + 1, bufB);
+        }
       }
     }
 
@@ -291,7 +363,36 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       uint32_t r[32];
       const int quarter = warp & 3, cblk = warp >> 2;  // TMEM lanes 32*quarter.., and which columns this warp drains
-      if (D == 64) {
+      if (STACK) {
+        // G = HH + LH + LH^T: LH goes through shared memory (the ring is idle: every MMA of the sub-segment has completed
+        // and no producer passes the closing barrier before all have finished reading)
+        constexpr int LDS_ = D + 1;
+        float* lh = reinterpret_cast<float*>(tiles);
+        const int c0 = 32 * cblk;
+        {
+          // lanes 0-63: HH rows, lanes 64-127: LH rows; two column blocks of 32
+          if (cblk < 2 && quarter >= 2) {
+            tmem_ld32(tmem + ((uint32_t)(32 * quarter) << 16) + c0, r);
+            const int m = 32 * (quarter - 2) + lane;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) lh[m * LDS_ + c0 + e] = __uint_as_float(r[e]);
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(kUmmaThreads) : "memory");
+          if (cblk < 2 && quarter < 2) {
+            tmem_ld32(tmem + ((uint32_t)(32 * quarter) << 16) + c0, r);
+            const int m = 32 * quarter + lane;
+            float4* dst = reinterpret_cast<float4*>(G + (size_t)m * D + c0);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              float o[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                o[e] = __uint_as_float(r[4 * q + e]) + (lh[m * LDS_ + c0 + 4 * q + e] + lh[(c0 + 4 * q + e) * LDS_ + m]);
+              dst[q] = make_float4(o[0], o[1], o[2], o[3]);
+            }
+          }
+        }
+      } else if (D == 64) {
         // M = 64: accumulator row m sits in TMEM lane (m & 15) + 32 * (m >> 4): lanes 0-15 of every quarter
         if (cblk < 2) {
           const int c0 = 32 * cblk;
