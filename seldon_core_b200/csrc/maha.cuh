@@ -33,6 +33,12 @@ constexpr int kMaxKP = 32;
 
 SubLayout make_layout(int64_t rows);
 int64_t max_subsegments(int64_t max_rows);
+// Split pass 2 takes the per-sub-segment statistics from its own projection kernel, not from the pass-1 partials, so it
+// cuts the rows independently and finer: chain4 runs 8 chains per warp and wants kTargetChains2 of them in flight.
+constexpr int kTargetChains2 = kNumSMs * 64;  // 2 CTAs x 4 warps x 8 chains per SM
+constexpr int kMinSubLen2 = 256;
+SubLayout make_layout2(int64_t rows);
+int64_t max_subsegments2(int64_t max_rows);
 
 constexpr int SUBFLAG_OPEN = 1;  // warm-up gate test passes at the first row of the sub-segment
 constexpr int SUBFLAG_WELL = 2;  // start matrix well enough conditioned for the fp32 chain
@@ -80,7 +86,8 @@ struct sb_maha {
   int64_t rows_local, rows_total, row0, n_eff;
   int use_clip;
   int split_pass2;  // decided in pass 1: projection kernel + chain kernel (d = 64/128/256, k <= 16, aligned rows)
-  sb::SubLayout lay;
+  sb::SubLayout lay;   // pass 1 (and the non-split pass 2)
+  sb::SubLayout lay2;  // split pass 2
   // options
   int gram_terms, force_generic, profile, fused_pass2, legacy_mma;
   cudaEvent_t ev[10];  // profile: [0,1] pass-1 kernel, [2,3] eigh, [4,5] prefix kernels, [6,7] projection, [8,9] chain

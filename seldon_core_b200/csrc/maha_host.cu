@@ -14,7 +14,8 @@ namespace {
 int padded_k(int k) { return k <= 4 ? 4 : k <= 8 ? 8 : k <= 16 ? 16 : 32; }
 
 // carve the caller's workspace; returns the total number of bytes needed for `nsub_max` sub-segments
-uint64_t carve(const sb_maha* h, int64_t nsub_max, int64_t rows_max, void* base, MahaWs* ws) {
+// (pass-1 layout) and `nsub2_max` (split pass-2 layout)
+uint64_t carve(const sb_maha* h, int64_t nsub_max, int64_t nsub2_max, int64_t rows_max, void* base, MahaWs* ws) {
   const uint64_t d = h->d, KP = h->KP, KQ = KP + KP * KP, PS = d + d * d, SL = 1 + PS;
   uint64_t off = 0;
   auto take = [&](uint64_t bytes) {
@@ -22,17 +23,18 @@ uint64_t carve(const sb_maha* h, int64_t nsub_max, int64_t rows_max, void* base,
     off = align_up(off + bytes, 256);
     return o;
   };
+  const bool split = (h->d == 64 || h->d == 128 || h->d == 256) && h->KP == 16;
+  if (!split || nsub2_max < nsub_max) nsub2_max = nsub_max;
   uint64_t o_part = take((uint64_t)nsub_max * PS * sizeof(float));
-  uint64_t o_proj = take((uint64_t)(nsub_max + 1) * KQ * sizeof(double));
-  uint64_t o_P = take((uint64_t)nsub_max * KP * KP * sizeof(float));
-  uint64_t o_Z = take((uint64_t)nsub_max * KP * sizeof(float));
-  uint64_t o_fl = take((uint64_t)nsub_max * sizeof(int32_t));
+  uint64_t o_proj = take((uint64_t)(nsub2_max + 1) * KQ * sizeof(double));
+  uint64_t o_P = take((uint64_t)nsub2_max * KP * KP * sizeof(float));
+  uint64_t o_Z = take((uint64_t)nsub2_max * KP * sizeof(float));
+  uint64_t o_fl = take((uint64_t)nsub2_max * sizeof(int32_t));
   uint64_t o_st = take(SL * sizeof(double));
   uint64_t o_pre = take(SL * sizeof(double));
   uint64_t o_rp = take(KQ * sizeof(double));
   uint64_t o_sl = take((uint64_t)reduce_slices((int)d) * PS * sizeof(double));
-  uint64_t o_ct = take((uint64_t)(nsub_max / 32 + 2) * KQ * sizeof(double));
-  const bool split = (h->d == 64 || h->d == 128 || h->d == 256) && h->KP == 16;
+  uint64_t o_ct = take((uint64_t)(nsub2_max / 32 + 2) * KQ * sizeof(double));
   uint64_t o_pz = take(split ? (uint64_t)rows_max * 16 * sizeof(float) : 0);
   uint64_t o_pd = take(split ? (uint64_t)rows_max * 16 * sizeof(float) : 0);
   uint64_t o_pf = take(split ? (uint64_t)rows_max : 0);
@@ -79,8 +81,7 @@ int refresh_float_state(sb_maha* h, cudaStream_t st) {
 
 int get_ws(const sb_maha* h, int64_t rows, void* d_ws, uint64_t ws_bytes, MahaWs* ws) {
   SB_REQUIRE(d_ws != nullptr && ((uintptr_t)d_ws & 255) == 0, SB_ERR_INVALID, "workspace must be 256-byte aligned");
-  const int64_t nsub = make_layout(rows).nsub;
-  uint64_t need = carve(h, nsub, rows, d_ws, ws);
+  uint64_t need = carve(h, make_layout(rows).nsub, make_layout2(rows).nsub, rows, d_ws, ws);
   SB_REQUIRE(need <= ws_bytes, SB_ERR_WORKSPACE, "workspace too small: need %llu bytes, got %llu",
              (unsigned long long)need, (unsigned long long)ws_bytes);
   return SB_OK;
@@ -140,7 +141,7 @@ extern "C" int32_t sb_maha_destroy(sb_maha_t* h) {
 
 extern "C" int32_t sb_maha_workspace_bytes(const sb_maha_t* h, int64_t max_rows, uint64_t* bytes) {
   SB_REQUIRE(h && bytes && max_rows >= 1, SB_ERR_INVALID, "sb_maha_workspace_bytes: bad arguments");
-  *bytes = carve(h, max_subsegments(max_rows), max_rows, nullptr, nullptr);
+  *bytes = carve(h, max_subsegments(max_rows), max_subsegments2(max_rows), max_rows, nullptr, nullptr);
   return SB_OK;
 }
 
@@ -182,6 +183,7 @@ extern "C" int32_t sb_maha_pass1_stats(sb_maha_t* h, const float* d_X, int64_t r
   h->use_clip = (h->n > h->start_clip) && h->has_clip;               // L85 (uncapped n)
   h->split_pass2 = h->KP == 16 && (h->d == 64 || h->d == 128 || h->d == 256) && !h->force_generic &&
                    !h->fused_pass2 && (ld % 4 == 0) && (((uintptr_t)d_X & 15) == 0);
+  h->lay2 = h->split_pass2 ? make_layout2(rows) : h->lay;
   if ((rc = launch_pass1(h, d_X, ld, ws, st))) return rc;
   if ((rc = launch_reduce(h, ws, d_stats_out ? d_stats_out : ws.stats, st))) return rc;
   h->stage = 1;

@@ -532,11 +532,9 @@ score_chain(const float* __restrict__ X, int64_t ld, int d, SubLayout lay, const
 }
 
 // ------------------------------------------------------------------------------- d = 64, KP = 16, tensor cores
-__device__ __forceinline__ uint32_t to_tf32(float x) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return r;
-}
+// round to nearest (ties away) to the TF32 mantissa with integer arithmetic: the value cvt.rna.tf32.f32 gives for finite
+// inputs, in two instructions (ptxas expands the cvt into about six on sm_100a)
+__device__ __forceinline__ uint32_t to_tf32(float x) { return (__float_as_uint(x) + 0x1000u) & 0xffffe000u; }
 __device__ __forceinline__ void mma_m16n8k8_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                                  uint32_t b0, uint32_t b1) {
   asm volatile(
@@ -604,8 +602,8 @@ struct BlockPos {  // the 16-row block a group works on
 
 // next block of the same sub-segment, or the first block of the next sub-segment assigned to this group
 __device__ __forceinline__ BlockPos next_block(BlockPos p, int stride, const SubLayout& lay, int bstar,
-                                               const int32_t* __restrict__ sub_flags) {
-  p.r += 16;
+                                               const int32_t* __restrict__ sub_flags, int step = 16) {
+  p.r += step;
   while (p.sub < lay.nsub && p.r >= p.r_end) {
     p.sub += stride;
     if (p.sub >= lay.nsub) break;
@@ -992,14 +990,15 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
           const float4 h4 = *reinterpret_cast<const float4*>(his + cbase);
           const float ll[4] = {l4.x, l4.y, l4.z, l4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w};
           float ca[4], cb[4];
-          bool anyc = false;
+          uint32_t diff = 0;  // any bit that clipping changed (one LOP3 per element)
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             ca[e] = fminf(fmaxf(ra[q][e], ll[e]), hh[e]);
             cb[e] = fminf(fmaxf(rbv[q][e], ll[e]), hh[e]);
-            anyc = anyc || (ca[e] != ra[q][e]) || (cb[e] != rbv[q][e]);
+            diff |= __float_as_uint(ca[e]) ^ __float_as_uint(ra[q][e]);
+            diff |= __float_as_uint(cb[e]) ^ __float_as_uint(rbv[q][e]);
           }
-          if (anyc) {  // rare: list the clipped elements of this lane
+          if (diff != 0) {  // rare: list the clipped elements of this lane
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
 #pragma unroll
@@ -1311,6 +1310,299 @@ chain16(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_
   }
 }
 
+// chain4: the same recurrence as chain16 with FOUR lanes per sub-segment (lane l owns rows 4l..4l+3 of S^-1 = 64
+// registers), eight sub-segments per warp and blocks of 8 rows.  Per chain and step this needs about half the warp
+// instructions of chain16: the matrix-vector products and the rank-2 update are the same FFMA2 count, but the shuffle
+// butterflies are two rounds instead of four and are shared by four times as many chains, and the operand loads
+// (e, c) are shared by eight chains.  Clipped rows use the expansion
+//     u^T P u = e^T P e + 2 dl.(P e) + dl.(P dl),   dl = y - z = V^T(x - clip(x)),
+// so only P dl is computed in addition (and only for the row of the pair that needs it).
+constexpr int kChain4Rows = 8;
+template <bool CLIP>
+__global__ void __launch_bounds__(128, 2)
+chain4(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t* __restrict__ cflag, SubLayout lay,
+       const float* __restrict__ sub_P, const float* __restrict__ sub_Z, const int32_t* __restrict__ sub_flags,
+       long long n_eff, long long row0, double threshold, long long* __restrict__ gate,
+       double* __restrict__ score_sum, float* __restrict__ score, int32_t* __restrict__ flag) {
+  constexpr int KP = 16, RB = kChain4Rows;
+  // per-chain strides are padded by 16 bytes: the eight chains of a warp read the same offsets of their own buffers
+  // in one LDS.128, and unpadded strides (512 B, 256 B) would put all eight in the same banks
+  constexpr int ES = RB * KP + 4, CS = 2 * 2 * KP + 4;
+  extern __shared__ __align__(16) float chain4_smem[];
+  float* ebuf = chain4_smem;                    // [32 chains][ES]       e of the block being walked
+  float* cbufs = ebuf + 32 * ES;                // [32][CS]              c1 | c2, two parities
+  float* dbuf = cbufs + 32 * CS;                // [2][32][ES]  (CLIP)   y - z, zero for rows without a clipped feature
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int l = lane & 3, ci = warp * 8 + (lane >> 2);
+  float* eb = ebuf + ci * ES;
+  const int chains_total = gridDim.x * 32;
+  const int bstar = (int)gate[0];
+
+  float2 P[4][8];
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) P[q][i] = make_float2(0.f, 0.f);
+  float4 Zrun = make_float4(0.f, 0.f, 0.f, 0.f);
+  BlockPos cur{(int)(blockIdx.x * 32 + ci) - chains_total, 0, 0};
+  cur.r = -RB;
+  cur = next_block(cur, chains_total, lay, bstar, sub_flags, RB);
+  int loaded_sub = -1;
+  long long nf = 0;
+  double ss = 0.0;
+  // Software pipeline over the blocks of a chain: the clip flags are fetched two blocks ahead, the rows (z) one block
+  // ahead into registers, the clip corrections (y - z, only rows whose flag is set; the others are zero-filled) one
+  // block ahead with cp.async into the other half of dbuf.
+  auto rows_of = [&](const BlockPos& p) { return p.sub < lay.nsub ? (int)min((int64_t)RB, p.r_end - p.r) : 0; };
+  auto load_flags = [&](const BlockPos& p) {  // eight flag bytes of the block, raw
+    uint2 fb = make_uint2(0u, 0u);
+    const int na = rows_of(p);
+    if (CLIP && na > 0) {
+      if (na == RB) {
+        fb = __ldg(reinterpret_cast<const uint2*>(cflag + p.r));  // block starts are multiples of 8
+      } else {
+        for (int rr = 0; rr < na; ++rr) {
+          const unsigned b = cflag[p.r + rr] != 0 ? 1u : 0u;
+          if (rr < 4) fb.x |= b << (8 * rr); else fb.y |= b << (8 * (rr - 4));
+        }
+      }
+    }
+    return fb;
+  };
+  auto flag_mask = [](uint2 fb) {  // bit r = row r has a clipped feature
+    return ((fb.x | (fb.x >> 7) | (fb.x >> 14) | (fb.x >> 21)) & 0xfu) |
+           (((fb.y | (fb.y >> 7) | (fb.y >> 14) | (fb.y >> 21)) & 0xfu) << 4);
+  };
+  auto load_rows = [&](const BlockPos& p, float4 (&z)[RB]) {
+    const int na = rows_of(p);
+#pragma unroll
+    for (int rr = 0; rr < RB; ++rr)
+      z[rr] = rr < na ? __ldg(reinterpret_cast<const float4*>(Zp + (p.r + rr) * KP) + l) : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (na > 0 && p.r + 2 * RB < p.r_end)  // two blocks further on towards L2 (512 B = four lines, one per lane)
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(Zp + (p.r + 2 * RB) * KP + 32 * l));
+  };
+  auto fetch_corr = [&](const BlockPos& p, unsigned cm, int half) {  // this lane's 16 bytes of every row of the block
+    if (!CLIP) return;
+    if (__any_sync(0xffffffffu, cm != 0)) {
+      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(dbuf + (half * 32 + ci) * ES + 4 * l);
+#pragma unroll
+      for (int rr = 0; rr < RB; ++rr) {
+        const bool on = (cm >> rr) & 1u;
+        const float* src = on ? Dp + (p.r + rr) * KP + 4 * l : Dp;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + rr * KP * 4), "l"(src), "r"(on ? 16 : 0) : "memory");
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  BlockPos nxt = cur.sub < lay.nsub ? next_block(cur, chains_total, lay, bstar, sub_flags, RB) : cur;
+  uint2 fb_cur = load_flags(cur), fb_nxt = load_flags(nxt);
+  float4 zr[RB];
+  load_rows(cur, zr);
+  int par = 0;
+  fetch_corr(cur, flag_mask(fb_cur), par);
+  while (__any_sync(0xffffffffu, cur.sub < lay.nsub)) {
+    const bool have = cur.sub < lay.nsub;
+    const int64_t rb = cur.r;
+    const int nact = rows_of(cur);  // active rows of this block
+    const unsigned cmask_cur = flag_mask(fb_cur), cmask_nxt = flag_mask(fb_nxt);
+    const BlockPos nxt2 = nxt.sub < lay.nsub ? next_block(nxt, chains_total, lay, bstar, sub_flags, RB) : nxt;
+    const uint2 fb_nxt2 = load_flags(nxt2);
+    if (have && cur.sub != loaded_sub) {
+      const float4* src4 = reinterpret_cast<const float4*>(sub_P + (size_t)cur.sub * KP * KP + (size_t)(4 * l) * KP);
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int i4 = 0; i4 < 4; ++i4) {
+          const float4 v = src4[q * 4 + i4];
+          P[q][2 * i4] = make_float2(v.x, v.y);
+          P[q][2 * i4 + 1] = make_float2(v.z, v.w);
+        }
+      Zrun = *reinterpret_cast<const float4*>(sub_Z + (size_t)cur.sub * KP + 4 * l);
+      loaded_sub = cur.sub;
+    }
+    // deviations of the whole block from the running prefix: e_i = z_i - Z_i/(n+i)
+    const bool blk_clip = CLIP && __any_sync(0xffffffffu, cmask_cur != 0);
+    const float* db = dbuf + (par * 32 + ci) * ES;
+    const double nb = (double)(n_eff + row0 + rb);
+    float invr[RB];
+#pragma unroll
+    for (int rr = 0; rr < RB; ++rr) {
+      const float ni = (float)(nb + (double)rr);
+      const float inv = (rr < nact && ni > 0.f) ? __fdividef(1.f, ni) : 0.f;
+      invr[rr] = inv;
+      const float4 z = zr[rr];
+      float4 e;
+      e.x = fmaf(-Zrun.x, inv, z.x); e.y = fmaf(-Zrun.y, inv, z.y);
+      e.z = fmaf(-Zrun.z, inv, z.z); e.w = fmaf(-Zrun.w, inv, z.w);
+      if (rr >= nact) e = make_float4(0.f, 0.f, 0.f, 0.f);
+      Zrun.x += z.x; Zrun.y += z.y; Zrun.z += z.z; Zrun.w += z.w;
+      *reinterpret_cast<float4*>(eb + rr * KP + 4 * l) = e;
+    }
+    // the next block's rows and corrections travel while this block is walked
+    fetch_corr(nxt, cmask_nxt, par ^ 1);
+    load_rows(nxt, zr);
+    asm volatile("cp.async.wait_group 1;" ::: "memory");  // this block's corrections have landed
+    __syncwarp();
+    float sc0 = 0.f, sc1 = 0.f;
+#pragma unroll
+    for (int pr = 0; pr < RB / 2; ++pr) {
+      const int r1 = 2 * pr, r2 = 2 * pr + 1;
+      const float4* e1p = reinterpret_cast<const float4*>(eb + r1 * KP);
+      const float4* e2p = reinterpret_cast<const float4*>(eb + r2 * KP);
+      float2 ca[4], da[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) ca[q] = da[q] = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int i4 = 0; i4 < 4; ++i4) {
+        const float4 x = e1p[i4], y = e2p[i4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          ca[q] = ffma2(P[q][2 * i4], make_float2(x.x, x.y), ca[q]);
+          ca[q] = ffma2(P[q][2 * i4 + 1], make_float2(x.z, x.w), ca[q]);
+          da[q] = ffma2(P[q][2 * i4], make_float2(y.x, y.y), da[q]);
+          da[q] = ffma2(P[q][2 * i4 + 1], make_float2(y.z, y.w), da[q]);
+        }
+      }
+      float c1[4], d2[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { c1[q] = ca[q].x + ca[q].y; d2[q] = da[q].x + da[q].y; }
+      const float4 e1m = e1p[l], e2m = e2p[l];  // this lane's four components of e1, e2
+      float t11 = fmaf(e1m.x, c1[0], fmaf(e1m.y, c1[1], fmaf(e1m.z, c1[2], e1m.w * c1[3])));
+      float t12 = fmaf(e1m.x, d2[0], fmaf(e1m.y, d2[1], fmaf(e1m.z, d2[2], e1m.w * d2[3])));
+      float t22 = fmaf(e2m.x, d2[0], fmaf(e2m.y, d2[1], fmaf(e2m.z, d2[2], e2m.w * d2[3])));
+#pragma unroll
+      for (int o = 1; o <= 2; o <<= 1) {
+        t11 += __shfl_xor_sync(0xffffffffu, t11, o);
+        t12 += __shfl_xor_sync(0xffffffffu, t12, o);
+        t22 += __shfl_xor_sync(0xffffffffu, t22, o);
+      }
+      // g = w/(1 + w t) with w = (n+i)/(n+i+1)  ==  1/(1 + 1/(n+i) + t)
+      const float g1 = invr[r1] > 0.f ? __fdividef(1.f, 1.f + invr[r1] + t11) : 0.f;
+      const float k12 = g1 * t12;
+      float c2[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) c2[q] = fmaf(-k12, c1[q], d2[q]);
+      const float t2 = fmaf(-k12, t12, t22);
+      const float g2 = invr[r2] > 0.f ? __fdividef(1.f, 1.f + invr[r2] + t2) : 0.f;
+      float q1 = t11, q2 = t2;
+      if (CLIP && blk_clip) {
+        const bool f1 = __any_sync(0xffffffffu, ((cmask_cur >> r1) & 1u) != 0);
+        const bool f2 = __any_sync(0xffffffffu, ((cmask_cur >> r2) & 1u) != 0);
+        if (f1 || f2) {  // warp-uniform
+          float a11 = 0.f, b11 = 0.f, a22 = 0.f, b22 = 0.f, x12 = 0.f;
+          if (f1) {
+            const float4* dp = reinterpret_cast<const float4*>(db + r1 * KP);
+            float2 pa[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) pa[q] = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int i4 = 0; i4 < 4; ++i4) {
+              const float4 x = dp[i4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                pa[q] = ffma2(P[q][2 * i4], make_float2(x.x, x.y), pa[q]);
+                pa[q] = ffma2(P[q][2 * i4 + 1], make_float2(x.z, x.w), pa[q]);
+              }
+            }
+            const float4 dm = dp[l];
+            a11 = fmaf(dm.x, c1[0], fmaf(dm.y, c1[1], fmaf(dm.z, c1[2], dm.w * c1[3])));
+            b11 = fmaf(dm.x, pa[0].x + pa[0].y, fmaf(dm.y, pa[1].x + pa[1].y,
+                       fmaf(dm.z, pa[2].x + pa[2].y, dm.w * (pa[3].x + pa[3].y))));
+          }
+          if (f2) {
+            const float4* dp = reinterpret_cast<const float4*>(db + r2 * KP);
+            float2 pa[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) pa[q] = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int i4 = 0; i4 < 4; ++i4) {
+              const float4 x = dp[i4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                pa[q] = ffma2(P[q][2 * i4], make_float2(x.x, x.y), pa[q]);
+                pa[q] = ffma2(P[q][2 * i4 + 1], make_float2(x.z, x.w), pa[q]);
+              }
+            }
+            const float4 dm = dp[l];
+            a22 = fmaf(dm.x, d2[0], fmaf(dm.y, d2[1], fmaf(dm.z, d2[2], dm.w * d2[3])));
+            x12 = fmaf(dm.x, c1[0], fmaf(dm.y, c1[1], fmaf(dm.z, c1[2], dm.w * c1[3])));
+            b22 = fmaf(dm.x, pa[0].x + pa[0].y, fmaf(dm.y, pa[1].x + pa[1].y,
+                       fmaf(dm.z, pa[2].x + pa[2].y, dm.w * (pa[3].x + pa[3].y))));
+          }
+#pragma unroll
+          for (int o = 1; o <= 2; o <<= 1) {
+            a11 += __shfl_xor_sync(0xffffffffu, a11, o);
+            b11 += __shfl_xor_sync(0xffffffffu, b11, o);
+            a22 += __shfl_xor_sync(0xffffffffu, a22, o);
+            b22 += __shfl_xor_sync(0xffffffffu, b22, o);
+            x12 += __shfl_xor_sync(0xffffffffu, x12, o);
+          }
+          q1 = t11 + fmaf(2.f, a11, b11);
+          const float cu = t12 + x12;  // c1 . u2
+          q2 = fmaf(-g1 * cu, cu, t22 + fmaf(2.f, a22, b22));
+        }
+      }
+      if (pr == l) { sc0 = q1; sc1 = q2; }
+      // broadcast c1, c2 and apply both rank-1 terms to this lane's rows of P
+      float* cb = cbufs + ci * CS + (pr & 1) * 2 * KP;
+      *reinterpret_cast<float4*>(cb + 4 * l) = make_float4(c1[0], c1[1], c1[2], c1[3]);
+      *reinterpret_cast<float4*>(cb + KP + 4 * l) = make_float4(c2[0], c2[1], c2[2], c2[3]);
+      __syncwarp();
+      float2 n1[4], n2[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        n1[q] = make_float2(-g1 * c1[q], -g1 * c1[q]);
+        n2[q] = make_float2(-g2 * c2[q], -g2 * c2[q]);
+      }
+#pragma unroll
+      for (int i4 = 0; i4 < 4; ++i4) {
+        const float4 x1 = *reinterpret_cast<const float4*>(cb + 4 * i4);
+        const float4 x2 = *reinterpret_cast<const float4*>(cb + KP + 4 * i4);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          P[q][2 * i4] = ffma2(n1[q], make_float2(x1.x, x1.y), P[q][2 * i4]);
+          P[q][2 * i4 + 1] = ffma2(n1[q], make_float2(x1.z, x1.w), P[q][2 * i4 + 1]);
+          P[q][2 * i4] = ffma2(n2[q], make_float2(x2.x, x2.y), P[q][2 * i4]);
+          P[q][2 * i4 + 1] = ffma2(n2[q], make_float2(x2.z, x2.w), P[q][2 * i4 + 1]);
+        }
+      }
+    }
+    // lane l holds the quadratic forms of rows 2l and 2l+1 of the block
+    {
+      const int ra = 2 * l;
+      const float s0 = ((float)(nb + (double)ra) - 1.f) * sc0;
+      const float s1 = ((float)(nb + (double)(ra + 1)) - 1.f) * sc1;
+      const int f0 = (double)s0 > threshold, f1 = (double)s1 > threshold;
+      if (ra + 1 < nact) {
+        *reinterpret_cast<float2*>(score + rb + ra) = make_float2(s0, s1);
+        *reinterpret_cast<int2*>(flag + rb + ra) = make_int2(f0, f1);
+        nf += f0 + f1;
+        ss += (double)s0 + (double)s1;
+      } else if (ra < nact) {
+        score[rb + ra] = s0;
+        flag[rb + ra] = f0;
+        nf += f0;
+        ss += (double)s0;
+      }
+    }
+    cur = nxt;
+    nxt = nxt2;
+    fb_cur = fb_nxt;
+    fb_nxt = fb_nxt2;
+    par ^= 1;
+  }
+  asm volatile("cp.async.wait_all;" ::: "memory");
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    nf += __shfl_xor_sync(0xffffffffu, nf, o);
+    ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  }
+  if (lane == 0 && (nf != 0 || ss != 0.0)) {
+    atomicAdd((unsigned long long*)(gate + 2), (unsigned long long)nf);
+    atomicAdd(score_sum, ss);
+  }
+}
+
 // PC0 = V^T C0 V (KP x KP, zero padded), one block
 __global__ void __launch_bounds__(256)
 project_cov(const double* __restrict__ C0, const double* __restrict__ V, int d, int KP, double* __restrict__ PC0) {
@@ -1368,8 +1660,9 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
 template <int KP>
 int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_t* flag, const MahaWs& ws,
                     cudaStream_t st) {
-  const int d = h->d, nsub = h->lay.nsub;
-  const SubLayout& L = h->lay;
+  const int d = h->d;
+  const SubLayout& L = h->split_pass2 ? h->lay2 : h->lay;
+  const int nsub = L.nsub;
   const bool aligned = (ld % 4 == 0) && (((uintptr_t)X & 15) == 0);
   const bool fast = KP == 16 && d == 64 && !h->force_generic && aligned;
   const bool split = h->split_pass2 != 0;
@@ -1428,16 +1721,21 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
   if (h->profile) cudaEventRecord(h->ev[8], st);
   if (split) {
     if constexpr (KP == 16) {
-      int cgrid = (int)ceil_div(nsub, 16);
+      int cgrid = (int)ceil_div(nsub, 32);
       if (cgrid > kNumSMs * 2) cgrid = kNumSMs * 2;
-      if (h->use_clip)
-        chain16<true><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
-                                            (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
-                                            h->d_score_sum, score, flag);
-      else
-        chain16<false><<<cgrid, 256, 0, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
+      constexpr int ES = kChain4Rows * 16 + 4, CS = 2 * 2 * 16 + 4;
+      if (h->use_clip) {
+        const size_t csm = (size_t)(32 * ES + 32 * CS + 2 * 32 * ES) * sizeof(float);
+        SB_CUDA(cudaFuncSetAttribute(chain4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csm));
+        chain4<true><<<cgrid, 128, csm, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
                                              (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
                                              h->d_score_sum, score, flag);
+      } else {
+        const size_t csm = (size_t)(32 * ES + 32 * CS) * sizeof(float);
+        chain4<false><<<cgrid, 128, csm, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
+                                              (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
+                                              h->d_score_sum, score, flag);
+      }
     }
   } else if (fast) {
     if constexpr (KP == 16) {

@@ -20,42 +20,45 @@
 
 namespace sb {
 
-SubLayout make_layout(int64_t rows) {
+namespace {
+SubLayout layout_for(int64_t rows, int64_t target, int64_t minlen) {
   SubLayout L{};
   L.rows = rows;
   L.shortlen = kShortLen;
   L.nshort = rows >= 8 * kShortLen ? 2 : 0;
   int64_t rest = rows - (int64_t)L.nshort * L.shortlen;
   if (rest <= 0) {
-    L.sublen = kMinSubLen;
+    L.sublen = minlen;
     L.nsub = L.nshort;
     return L;
   }
-  int64_t m = ceil_div(rest, (int64_t)kTargetChains * kMaxSubLen);
-  int64_t len = ceil_div(rest, (int64_t)kTargetChains * m);
+  int64_t m = ceil_div(rest, target * kMaxSubLen);
+  int64_t len = ceil_div(rest, target * m);
   len = ceil_div(len, 16) * 16;
-  if (len < kMinSubLen) len = kMinSubLen;
+  if (len < minlen) len = minlen;
   L.sublen = len;
   L.nsub = L.nshort + (int32_t)ceil_div(rest, len);
   return L;
 }
-
-int64_t max_subsegments(int64_t max_rows) {
-  // make_layout never produces more than kTargetChains*m + nshort sub-segments, m as computed for max_rows
-  int64_t m = ceil_div(max_rows > 0 ? max_rows : 1, (int64_t)kTargetChains * kMaxSubLen);
-  int64_t a = (int64_t)kTargetChains * m + 4;
-  int64_t b = ceil_div(max_rows, kMinSubLen) + 4;
+int64_t max_subs_for(int64_t max_rows, int64_t target, int64_t minlen) {
+  // layout_for never produces more than target*m + nshort sub-segments, m as computed for max_rows
+  int64_t m = ceil_div(max_rows > 0 ? max_rows : 1, target * kMaxSubLen);
+  int64_t a = target * m + 4;
+  int64_t b = ceil_div(max_rows, minlen) + 4;
   return a < b ? a : b;
 }
+}  // namespace
+SubLayout make_layout(int64_t rows) { return layout_for(rows, kTargetChains, kMinSubLen); }
+int64_t max_subsegments(int64_t max_rows) { return max_subs_for(max_rows, kTargetChains, kMinSubLen); }
+SubLayout make_layout2(int64_t rows) { return layout_for(rows, kTargetChains2, kMinSubLen2); }
+int64_t max_subsegments2(int64_t max_rows) { return max_subs_for(max_rows, kTargetChains2, kMinSubLen2); }
 
 namespace {
 
 // ---------------------------------------------------------------------------------------- d = 64, tensor cores
-__device__ __forceinline__ uint32_t to_tf32(float x) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return r;
-}
+// round to nearest (ties away) to the TF32 mantissa with integer arithmetic: the value cvt.rna.tf32.f32 gives for finite
+// inputs, in two instructions (ptxas expands the cvt into about six on sm_100a)
+__device__ __forceinline__ uint32_t to_tf32(float x) { return (__float_as_uint(x) + 0x1000u) & 0xffffe000u; }
 __device__ __forceinline__ void mma_m16n8k8_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                                  uint32_t b0, uint32_t b1) {
   asm volatile(
