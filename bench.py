@@ -286,7 +286,7 @@ def main():
             dom = {"kernel": "pass1_gram_umma<64> (clip, row sums, 3xTF32 Gram on tcgen05.mma kind::tf32)", "ms": kern_ms[0],
                    "bytes": pass1_bytes, "traffic_key": "pass1_dram_bytes_per_launch"}
         else:
-            dom = {"kernel": "pass 2 = project_rows<2,clip> + chain16<clip> (project on mma.sync 3xTF32, inverse chain, score, flag)", "ms": pass2_ms,
+            dom = {"kernel": "pass 2 = project_rows<1,clip> + chain4<clip> (project on mma.sync 3xTF32, inverse chain, score, flag)", "ms": pass2_ms,
                    "bytes": chain_bytes, "traffic_key": "pass2_dram_bytes_per_launch"}
         traffic = None
         if os.path.isfile(tpath):

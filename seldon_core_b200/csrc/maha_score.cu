@@ -1076,14 +1076,17 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
 #pragma unroll
         for (int i = 0; i < 2; ++i) reinterpret_cast<float4*>(dt)[lane + 32 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
         __syncwarp();
-        // y - z = V^T(x - clip(x)); the two half-warps take alternate events, lane j adds component j
+        // y - z = V^T(x - clip(x)); lane (half, j) owns component j of rows 8 half .. 8 half + 7: no atomics
         const int half = lane >> 4, jj = lane & 15;
         if (nev <= kProjEvCap) {
           for (int k = 0; k < nev; ++k) {
             const float2 ev = evlist[k];
             const int rc = __float_as_int(ev.x), row = rc / D, col = rc - row * D;
             rowmask |= 1u << row;
-            if ((k & 1) == half) atomicAdd(dt + row * KP + jj, ev.y * Vs[col * KP + jj]);
+            if ((row >> 3) == half) {
+              float* acc = dt + row * KP + jj;
+              *acc = fmaf(ev.y, Vs[col * KP + jj], *acc);
+            }
           }
         } else {
           // more than kProjEvCap clipped elements in 16 rows (degenerate data): recompute the block densely
@@ -1100,9 +1103,10 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
           }
         }
         __syncwarp();
-        for (int row = 0; row < 16; ++row)
-          if ((rowmask >> row) & 1u)
-            if (lane < KP) Dout[(rb + row) * KP + lane] = dt[row * KP + lane];
+        for (unsigned m = rowmask; m != 0; m &= m - 1) {
+          const int row = __ffs(m) - 1;
+          if (lane < KP) Dout[(rb + row) * KP + lane] = dt[row * KP + lane];
+        }
         __syncwarp();
         if (lane == 0) evcnt[warp] = 0;
       }
@@ -1134,192 +1138,27 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
   (void)rows;
 }
 
-// chain over the projected rows: group of 16 lanes per sub-segment, lane j owns row j of S^-1.
-// Two rows per step (rank-2 form of the Sherman-Morrison update): with c1 = P e1, d2 = P e2 and the three dot
-// products t11 = e1.c1, t12 = e1.d2, t22 = e2.d2 (one 3-wide shuffle butterfly),
+// chain over the projected rows.  Two rows per step (rank-2 form of the Sherman-Morrison update): with c1 = P e1,
+// d2 = P e2 and the three dot products t11 = e1.c1, t12 = e1.d2, t22 = e2.d2 (one 3-wide shuffle butterfly),
 //     g1 = w1/(1 + w1 t11),  c2 = d2 - g1 t12 c1,  t2 = t22 - g1 t12^2,  g2 = w2/(1 + w2 t2),
-//     P <- P - g1 c1 c1^T - g2 c2 c2^T,   score1 = (n+i-1) t11,  score2 = (n+i) t2
-// (clipped rows use u = e + (y - z) in the quadratic forms: q11 = u1.P u1, score2 = q22 - g1 (c1.u2)^2).
-// All deviations e, u of a 16-row block are formed up front from the running prefix and parked in shared memory,
-// so a step needs a single warp synchronisation (for the c broadcast).
-template <bool CLIP>
-__global__ void __launch_bounds__(256, 2)
-chain16(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t* __restrict__ cflag, SubLayout lay,
-        const float* __restrict__ sub_P, const float* __restrict__ sub_Z, const int32_t* __restrict__ sub_flags,
-        long long n_eff, long long row0, double threshold, long long* __restrict__ gate,
-        double* __restrict__ score_sum, float* __restrict__ score, int32_t* __restrict__ flag) {
-  constexpr int KP = 16;
-  __shared__ __align__(16) float4 rowsc[16][16];          // [group in CTA][row]: 1/(n+i), (n+i)/(n+i+1), n+i-1
-  __shared__ __align__(16) float ebuf[16][16 * KP];       // [group][row][comp]  e
-  __shared__ __align__(16) float ubuf[16][CLIP ? 16 * KP : 4];
-  __shared__ __align__(16) float cbufs[16][2][2 * KP];    // [group][parity][c1 | c2]
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int j = lane & 15, grp = lane >> 4, gi = warp * 2 + grp;
-  float* eb = ebuf[gi];
-  float* ub = ubuf[gi];
-  const int groups_total = gridDim.x * 16;
-  const int gid = blockIdx.x * 16 + gi;
-  const int bstar = (int)gate[0];
-
-  float2 P[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) P[i] = make_float2(0.f, 0.f);
-  float Zrun = 0.f;
-  BlockPos cur{gid - groups_total, 0, 0};
-  cur.r = -16;
-  cur = next_block(cur, groups_total, lay, bstar, sub_flags);
-  int loaded_sub = -1;
-  long long nf = 0;
-  double ss = 0.0;
-  while (__any_sync(0xffffffffu, cur.sub < lay.nsub)) {
-    const bool have = cur.sub < lay.nsub;
-    const int64_t rb = cur.r;
-    const int nact = have ? (int)min((int64_t)16, cur.r_end - rb) : 0;  // active rows of this block
-    float er[16], dr[16];
-    unsigned cmask = 0;
-    if (CLIP) {
-      const bool mine = j < nact && cflag[rb + j] != 0;
-      const unsigned bal = __ballot_sync(0xffffffffu, mine);
-      cmask = (bal >> (16 * grp)) & 0xffffu;
-    }
-#pragma unroll
-    for (int rr = 0; rr < 16; ++rr) {
-      er[rr] = rr < nact ? __ldg(Zp + (rb + rr) * KP + j) : 0.f;
-      dr[rr] = (CLIP && ((cmask >> rr) & 1u)) ? __ldg(Dp + (rb + rr) * KP + j) : 0.f;
-    }
-    {
-      const float ni = (float)(double)(n_eff + row0 + rb + j);
-      rowsc[gi][j] = make_float4(ni > 0.f ? __fdividef(1.f, ni) : 0.f, __fdividef(ni, ni + 1.f), ni - 1.f, 0.f);
-    }
-    if (have && cur.sub != loaded_sub) {
-      const float4* src4 = reinterpret_cast<const float4*>(sub_P + (size_t)cur.sub * KP * KP + (size_t)j * KP);
-#pragma unroll
-      for (int i4 = 0; i4 < 4; ++i4) {
-        const float4 v = src4[i4];
-        P[2 * i4] = make_float2(v.x, v.y);
-        P[2 * i4 + 1] = make_float2(v.z, v.w);
-      }
-      Zrun = sub_Z[(size_t)cur.sub * KP + j];
-      loaded_sub = cur.sub;
-    }
-    __syncwarp();
-    // deviations of the whole block from the running prefix: e_i = z_i - Z_i/(n+i), u_i = e_i + (y_i - z_i)
-    const bool any_clip = CLIP && __any_sync(0xffffffffu, cmask != 0);
-#pragma unroll
-    for (int rr = 0; rr < 16; ++rr) {
-      const float inv = rowsc[gi][rr].x;
-      const float z = er[rr];
-      const float e = rr < nact ? fmaf(-Zrun, inv, z) : 0.f;
-      Zrun += z;
-      er[rr] = e;
-      eb[rr * KP + j] = e;
-      if (any_clip) ub[rr * KP + j] = e + dr[rr];
-    }
-    __syncwarp();
-    float mysc = 0.f;
-#pragma unroll
-    for (int pr = 0; pr < 8; ++pr) {
-      const int r1 = 2 * pr, r2 = 2 * pr + 1;
-      const float4 sA = rowsc[gi][r1], sB = rowsc[gi][r2];
-      float2 a0 = make_float2(0.f, 0.f), a1 = a0, b0 = a0, b1 = a0;
-#pragma unroll
-      for (int i4 = 0; i4 < 4; ++i4) {
-        const float4 e1 = *reinterpret_cast<const float4*>(eb + r1 * KP + 4 * i4);
-        const float4 e2 = *reinterpret_cast<const float4*>(eb + r2 * KP + 4 * i4);
-        a0 = ffma2(P[2 * i4], make_float2(e1.x, e1.y), a0);
-        a1 = ffma2(P[2 * i4 + 1], make_float2(e1.z, e1.w), a1);
-        b0 = ffma2(P[2 * i4], make_float2(e2.x, e2.y), b0);
-        b1 = ffma2(P[2 * i4 + 1], make_float2(e2.z, e2.w), b1);
-      }
-      const float c1 = (a0.x + a0.y) + (a1.x + a1.y);
-      const float d2 = (b0.x + b0.y) + (b1.x + b1.y);
-      float t11 = er[r1] * c1, t12 = er[r1] * d2, t22 = er[r2] * d2;
-#pragma unroll
-      for (int o = 8; o > 0; o >>= 1) {
-        t11 += __shfl_xor_sync(0xffffffffu, t11, o);
-        t12 += __shfl_xor_sync(0xffffffffu, t12, o);
-        t22 += __shfl_xor_sync(0xffffffffu, t22, o);
-      }
-      const float g1 = r1 < nact ? __fdividef(sA.y, fmaf(sA.y, t11, 1.f)) : 0.f;
-      const float k12 = g1 * t12;
-      const float c2 = fmaf(-k12, c1, d2);
-      const float t2 = fmaf(-k12, t12, t22);
-      const float g2 = r2 < nact ? __fdividef(sB.y, fmaf(sB.y, t2, 1.f)) : 0.f;
-      float q1 = t11, q2 = t2;
-      const bool pair_clip = CLIP && __any_sync(0xffffffffu, ((cmask >> r1) & 3u) != 0);
-      if (pair_clip) {  // warp-uniform: quadratic forms with u instead of e
-        float2 v0 = make_float2(0.f, 0.f), v1 = v0, w0 = v0, w1 = v0;
-        const float u1j = ub[r1 * KP + j], u2j = ub[r2 * KP + j];
-#pragma unroll
-        for (int i4 = 0; i4 < 4; ++i4) {
-          const float4 u1 = *reinterpret_cast<const float4*>(ub + r1 * KP + 4 * i4);
-          const float4 u2 = *reinterpret_cast<const float4*>(ub + r2 * KP + 4 * i4);
-          v0 = ffma2(P[2 * i4], make_float2(u1.x, u1.y), v0);
-          v1 = ffma2(P[2 * i4 + 1], make_float2(u1.z, u1.w), v1);
-          w0 = ffma2(P[2 * i4], make_float2(u2.x, u2.y), w0);
-          w1 = ffma2(P[2 * i4 + 1], make_float2(u2.z, u2.w), w1);
-        }
-        float q11 = u1j * ((v0.x + v0.y) + (v1.x + v1.y));
-        float q22 = u2j * ((w0.x + w0.y) + (w1.x + w1.y));
-        float x12 = c1 * u2j;
-#pragma unroll
-        for (int o = 8; o > 0; o >>= 1) {
-          q11 += __shfl_xor_sync(0xffffffffu, q11, o);
-          q22 += __shfl_xor_sync(0xffffffffu, q22, o);
-          x12 += __shfl_xor_sync(0xffffffffu, x12, o);
-        }
-        q1 = q11;
-        q2 = fmaf(-g1 * x12, x12, q22);
-      }
-      if (j == r1) mysc = sA.z * q1;
-      if (j == r2) mysc = sB.z * q2;
-      // broadcast c1, c2 and apply both rank-1 terms to row j of P
-      float* cb = cbufs[gi][pr & 1];
-      cb[j] = c1;
-      cb[KP + j] = c2;
-      __syncwarp();
-      const float2 n1 = make_float2(-g1 * c1, -g1 * c1), n2 = make_float2(-g2 * c2, -g2 * c2);
-#pragma unroll
-      for (int i4 = 0; i4 < 4; ++i4) {
-        const float4 x1 = *reinterpret_cast<const float4*>(cb + 4 * i4);
-        const float4 x2 = *reinterpret_cast<const float4*>(cb + KP + 4 * i4);
-        P[2 * i4] = ffma2(n1, make_float2(x1.x, x1.y), P[2 * i4]);
-        P[2 * i4 + 1] = ffma2(n1, make_float2(x1.z, x1.w), P[2 * i4 + 1]);
-        P[2 * i4] = ffma2(n2, make_float2(x2.x, x2.y), P[2 * i4]);
-        P[2 * i4 + 1] = ffma2(n2, make_float2(x2.z, x2.w), P[2 * i4 + 1]);
-      }
-    }
-    if (j < nact) {
-      score[rb + j] = mysc;
-      const int f = (double)mysc > threshold;
-      flag[rb + j] = f;
-      nf += f;
-      ss += (double)mysc;
-    }
-    __syncwarp();
-    if (have) cur = next_block(cur, groups_total, lay, bstar, sub_flags);
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    nf += __shfl_xor_sync(0xffffffffu, nf, o);
-    ss += __shfl_xor_sync(0xffffffffu, ss, o);
-  }
-  if (lane == 0 && (nf != 0 || ss != 0.0)) {
-    atomicAdd((unsigned long long*)(gate + 2), (unsigned long long)nf);
-    atomicAdd(score_sum, ss);
-  }
-}
-
-// chain4: the same recurrence as chain16 with FOUR lanes per sub-segment (lane l owns rows 4l..4l+3 of S^-1 = 64
-// registers), eight sub-segments per warp and blocks of 8 rows.  Per chain and step this needs about half the warp
-// instructions of chain16: the matrix-vector products and the rank-2 update are the same FFMA2 count, but the shuffle
-// butterflies are two rounds instead of four and are shared by four times as many chains, and the operand loads
-// (e, c) are shared by eight chains.  Clipped rows use the expansion
+//     P <- P - g1 c1 c1^T - g2 c2 c2^T,   score1 = (n+i-1) t11,  score2 = (n+i) t2.
+// All deviations e of a block are formed up front from the running prefix and parked in shared memory, so a step needs
+// a single warp synchronisation (for the c broadcast).
+// chain4: FOUR lanes per sub-segment (lane l owns rows 4l..4l+3 of S^-1 = 64 registers), eight sub-segments per warp,
+// blocks of 8 rows.  Compared with one lane per row of S^-1 (16 lanes per chain, the first version of this kernel) the
+// matrix-vector products and the rank-2 update are the same FFMA2 count, but the shuffle butterflies are two rounds
+// instead of four and are shared by four times as many chains, and the operand loads (e, c) are shared by eight chains:
+// about half the warp instructions per row.  Clipped rows use the expansion
 //     u^T P u = e^T P e + 2 dl.(P e) + dl.(P dl),   dl = y - z = V^T(x - clip(x)),
 // so only P dl is computed in addition (and only for the row of the pair that needs it).
 constexpr int kChain4Rows = 8;
+// 8 warps per SM = 2 per scheduler with up to 255 registers; 3 per scheduler (168 registers) spills the prefetched block
+// and was measured slower (1.12 ms against 0.85 ms for 16Mi rows)
+constexpr int kChain4Warps = 4;                    // warps per CTA
+constexpr int kChain4Ctas = 2;                     // CTAs per SM
+constexpr int kChain4Chains = 8 * kChain4Warps;    // chains per CTA
 template <bool CLIP>
-__global__ void __launch_bounds__(128, 2)
+__global__ void __launch_bounds__(32 * kChain4Warps, kChain4Ctas)
 chain4(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t* __restrict__ cflag, SubLayout lay,
        const float* __restrict__ sub_P, const float* __restrict__ sub_Z, const int32_t* __restrict__ sub_flags,
        long long n_eff, long long row0, double threshold, long long* __restrict__ gate,
@@ -1329,13 +1168,14 @@ chain4(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t
   // in one LDS.128, and unpadded strides (512 B, 256 B) would put all eight in the same banks
   constexpr int ES = RB * KP + 4, CS = 2 * 2 * KP + 4;
   extern __shared__ __align__(16) float chain4_smem[];
-  float* ebuf = chain4_smem;                    // [32 chains][ES]       e of the block being walked
-  float* cbufs = ebuf + 32 * ES;                // [32][CS]              c1 | c2, two parities
-  float* dbuf = cbufs + 32 * CS;                // [2][32][ES]  (CLIP)   y - z, zero for rows without a clipped feature
+  constexpr int NCH = kChain4Chains;
+  float* ebuf = chain4_smem;                    // [NCH chains][ES]      e of the block being walked
+  float* cbufs = ebuf + NCH * ES;               // [NCH][CS]             c1 | c2, two parities
+  float* dbuf = cbufs + NCH * CS;               // [2][NCH][ES] (CLIP)   y - z, zero for rows without a clipped feature
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int l = lane & 3, ci = warp * 8 + (lane >> 2);
   float* eb = ebuf + ci * ES;
-  const int chains_total = gridDim.x * 32;
+  const int chains_total = gridDim.x * NCH;
   const int bstar = (int)gate[0];
 
   float2 P[4][8];
@@ -1344,7 +1184,7 @@ chain4(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t
 #pragma unroll
     for (int i = 0; i < 8; ++i) P[q][i] = make_float2(0.f, 0.f);
   float4 Zrun = make_float4(0.f, 0.f, 0.f, 0.f);
-  BlockPos cur{(int)(blockIdx.x * 32 + ci) - chains_total, 0, 0};
+  BlockPos cur{(int)(blockIdx.x * NCH + ci) - chains_total, 0, 0};
   cur.r = -RB;
   cur = next_block(cur, chains_total, lay, bstar, sub_flags, RB);
   int loaded_sub = -1;
@@ -1384,7 +1224,7 @@ chain4(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t
   auto fetch_corr = [&](const BlockPos& p, unsigned cm, int half) {  // this lane's 16 bytes of every row of the block
     if (!CLIP) return;
     if (__any_sync(0xffffffffu, cm != 0)) {
-      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(dbuf + (half * 32 + ci) * ES + 4 * l);
+      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(dbuf + (half * NCH + ci) * ES + 4 * l);
 #pragma unroll
       for (int rr = 0; rr < RB; ++rr) {
         const bool on = (cm >> rr) & 1u;
@@ -1422,7 +1262,7 @@ chain4(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t
     }
     // deviations of the whole block from the running prefix: e_i = z_i - Z_i/(n+i)
     const bool blk_clip = CLIP && __any_sync(0xffffffffu, cmask_cur != 0);
-    const float* db = dbuf + (par * 32 + ci) * ES;
+    const float* db = dbuf + (par * NCH + ci) * ES;
     const double nb = (double)(n_eff + row0 + rb);
     float invr[RB];
 #pragma unroll
@@ -1721,20 +1561,20 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
   if (h->profile) cudaEventRecord(h->ev[8], st);
   if (split) {
     if constexpr (KP == 16) {
-      int cgrid = (int)ceil_div(nsub, 32);
-      if (cgrid > kNumSMs * 2) cgrid = kNumSMs * 2;
-      constexpr int ES = kChain4Rows * 16 + 4, CS = 2 * 2 * 16 + 4;
+      constexpr int NCH = kChain4Chains, ES = kChain4Rows * 16 + 4, CS = 2 * 2 * 16 + 4;
+      int cgrid = (int)ceil_div(nsub, NCH);
+      if (cgrid > kNumSMs * kChain4Ctas) cgrid = kNumSMs * kChain4Ctas;
       if (h->use_clip) {
-        const size_t csm = (size_t)(32 * ES + 32 * CS + 2 * 32 * ES) * sizeof(float);
+        const size_t csm = (size_t)(NCH * ES + NCH * CS + 2 * NCH * ES) * sizeof(float);
         SB_CUDA(cudaFuncSetAttribute(chain4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csm));
-        chain4<true><<<cgrid, 128, csm, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
-                                             (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
-                                             h->d_score_sum, score, flag);
+        chain4<true><<<cgrid, 32 * kChain4Warps, csm, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z,
+                                                           ws.sub_flags, (long long)h->n_eff, (long long)h->row0,
+                                                           h->threshold, h->d_gate, h->d_score_sum, score, flag);
       } else {
-        const size_t csm = (size_t)(32 * ES + 32 * CS) * sizeof(float);
-        chain4<false><<<cgrid, 128, csm, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z, ws.sub_flags,
-                                              (long long)h->n_eff, (long long)h->row0, h->threshold, h->d_gate,
-                                              h->d_score_sum, score, flag);
+        const size_t csm = (size_t)(NCH * ES + NCH * CS) * sizeof(float);
+        chain4<false><<<cgrid, 32 * kChain4Warps, csm, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z,
+                                                            ws.sub_flags, (long long)h->n_eff, (long long)h->row0,
+                                                            h->threshold, h->d_gate, h->d_score_sum, score, flag);
       }
     }
   } else if (fast) {
