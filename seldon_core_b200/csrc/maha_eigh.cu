@@ -18,6 +18,10 @@
 namespace sb {
 namespace {
 
+// pairs whose cos^2 is below this are in the quadratically convergent regime: after rotating them the remaining
+// cosines are of the order of cos^2 <= 1e-14, below the 1e-11 working threshold
+constexpr double kQuadCos2 = 1e-14;
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -43,16 +47,16 @@ jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, doub
     __syncthreads();
     for (int idx = tid; idx < d * d; idx += blockDim.x) {
       const int c = idx / d, r = idx - c * d;
-      const double* crow = C + (size_t)r * d;
       const double* vcol = V + (size_t)c * d;
       double acc = 0.0;
-      for (int g = 0; g < d; ++g) acc = fma(crow[g], vcol[g], acc);
+      // C is symmetric: C[g][r] instead of C[r][g] makes the lanes of a warp read consecutive addresses
+      for (int g = 0; g < d; ++g) acc = fma(C[(size_t)g * d + r], vcol[g], acc);
       W[idx] = acc;
     }
   } else {
     for (int idx = tid; idx < d * d; idx += blockDim.x) {
       int c = idx / d, r = idx - c * d;
-      W[idx] = C[(size_t)r * d + c];  // column c of C (C is symmetric; kept explicit)
+      W[idx] = C[idx];  // column c of C = row c (C is symmetric)
       V[idx] = r == c ? 1.0 : 0.0;
     }
   }
@@ -101,7 +105,9 @@ jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, doub
           vp[r] = cs * a - sn * b;
           vq[r] = sn * a + cs * b;
         }
-        if (lane == 0) rotated = 1;
+        // a sweep whose largest |cos| was below kQuadCos leaves residuals of about cos^2 (quadratic convergence): no
+        // confirming sweep is needed after it
+        if (lane == 0 && ga * ga > kQuadCos2 * (al * be)) rotated = 1;
       }
       __syncthreads();
     }
@@ -138,6 +144,174 @@ jacobi_topk(const double* __restrict__ C, int d, int k, int KP, double* gW, doub
 }
 
 
+// d = 64: the columns live in REGISTERS.  512 threads = 32 half-warps; half-warp h holds the two columns of its pair
+// (lane l: rows 4l..4l+3 of W and V of both columns = 16 doubles).  Odd-even transposition ordering with an
+// unconditional exchange after every rotation: step t pairs the positions (2h, 2h+1) for even t and (2h+1, 2h+2) for
+// odd t; after 64 steps the order of the columns is reversed and every pair has met exactly once (one sweep).  Between
+// two steps every half-warp keeps one column and passes the other to a neighbour through shared memory (1 KB written,
+// 1 KB read per half-warp and step, one __syncthreads), against four columns read and four written per rotation when
+// the matrices sit in shared memory; the three dot products take 4 shuffle rounds and serve two pairs per warp.
+__global__ void __launch_bounds__(512, 1)
+jacobi64_regs(const double* __restrict__ C, int k, int KP, double* __restrict__ Vd, float* __restrict__ Vf,
+              double* __restrict__ evals, long long* __restrict__ gate, double* __restrict__ Vfull, int warm) {
+  constexpr int D = 64, CS = 2 * D;  // a column slot: W rows 0..63, then V rows 0..63
+  extern __shared__ double S[];      // [64 slots][128]; slots 0..31 = bufE, 32..63 = bufO while the sweeps run
+  __shared__ int rotated[2];
+  __shared__ double norms[D];
+  const int tid = threadIdx.x, lane = tid & 31, hw = tid >> 4, l = tid & 15;
+  double* bufE = S;
+  double* bufO = S + 32 * CS;
+
+  for (int idx = tid; idx < D * D; idx += blockDim.x) {
+    const int c = idx >> 6, r = idx & 63;
+    S[c * CS + D + r] = warm ? Vfull[idx] : (r == c ? 1.0 : 0.0);
+  }
+  if (tid < 2) rotated[tid] = 0;
+  __syncthreads();
+  // W = C V (columns): C is staged in shared memory behind S; thread (r, cg) forms rows r of the eight columns
+  // 8 cg .. 8 cg + 7, so that C[g][r] (C is symmetric) is read once per g and conflict free
+  {
+    double* Cs = S + D * CS;
+    for (int idx = tid; idx < D * D; idx += blockDim.x) Cs[idx] = C[idx];
+    __syncthreads();
+    const int r = tid & 63, cg = tid >> 6;
+    double acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.0;
+    if (warm) {
+      for (int g = 0; g < D; ++g) {
+        const double cv = Cs[g * D + r];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fma(cv, S[(8 * cg + j) * CS + D + g], acc[j]);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = Cs[(8 * cg + j) * D + r];
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) S[(8 * cg + j) * CS + r] = acc[j];
+  }
+  __syncthreads();
+  double Xw[4], Xv[4], Yw[4], Yv[4];
+  auto load_col = [&](const double* slot, double (&w)[4], double (&v)[4]) {
+    const double2 a = *reinterpret_cast<const double2*>(slot + 4 * l), b = *reinterpret_cast<const double2*>(slot + 4 * l + 2);
+    const double2 c = *reinterpret_cast<const double2*>(slot + D + 4 * l), e = *reinterpret_cast<const double2*>(slot + D + 4 * l + 2);
+    w[0] = a.x; w[1] = a.y; w[2] = b.x; w[3] = b.y;
+    v[0] = c.x; v[1] = c.y; v[2] = e.x; v[3] = e.y;
+  };
+  auto store_col = [&](double* slot, const double (&w)[4], const double (&v)[4]) {
+    *reinterpret_cast<double2*>(slot + 4 * l) = make_double2(w[0], w[1]);
+    *reinterpret_cast<double2*>(slot + 4 * l + 2) = make_double2(w[2], w[3]);
+    *reinterpret_cast<double2*>(slot + D + 4 * l) = make_double2(v[0], v[1]);
+    *reinterpret_cast<double2*>(slot + D + 4 * l + 2) = make_double2(v[2], v[3]);
+  };
+  load_col(S + (2 * hw) * CS, Xw, Xv);
+  load_col(S + (2 * hw + 1) * CS, Yw, Yv);
+  __syncthreads();  // from here on S is the exchange buffer
+
+  // rotate the pair (X, Y) so that the W columns become orthogonal; returns whether a rotation was applied
+  auto rotate = [&](bool active) {
+    double al = 0.0, be = 0.0, ga = 0.0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      al = fma(Xw[i], Xw[i], al);
+      be = fma(Yw[i], Yw[i], be);
+      ga = fma(Xw[i], Yw[i], ga);
+    }
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) {
+      al += __shfl_xor_sync(0xffffffffu, al, o);
+      be += __shfl_xor_sync(0xffffffffu, be, o);
+      ga += __shfl_xor_sync(0xffffffffu, ga, o);
+    }
+    if (!active || al == 0.0 || be == 0.0) return false;
+    if (ga * ga <= 1e-22 * (al * be)) return false;  // |cos| <= 1e-11: orthogonal to working accuracy
+    const bool big = ga * ga > kQuadCos2 * (al * be);
+    // the rotation only has to be orthogonal to fp64 accuracy; its angle merely sets the convergence rate (fp32)
+    const float zeta = __fdividef((float)(be - al), (float)(2.0 * ga));
+    const float tf = __fdividef(copysignf(1.f, zeta), fabsf(zeta) + sqrtf(fmaf(zeta, zeta, 1.f)));
+    if (!(fabsf(tf) > 0.f)) return false;
+    const double tt = (double)tf;
+    const double hh = fma(tt, tt, 1.0);
+    double cs = (double)rsqrtf((float)hh);  // fp32 seed, two Newton steps -> full fp64 accuracy
+    cs = cs * fma(-0.5 * hh, cs * cs, 1.5);
+    cs = cs * fma(-0.5 * hh, cs * cs, 1.5);
+    const double sn = cs * tt;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      double a = Xw[i], b = Yw[i];
+      Xw[i] = cs * a - sn * b;
+      Yw[i] = sn * a + cs * b;
+      a = Xv[i]; b = Yv[i];
+      Xv[i] = cs * a - sn * b;
+      Yv[i] = sn * a + cs * b;
+    }
+    return big;  // small rotations do not call for another sweep
+  };
+
+  int sweeps = 0;
+  for (; sweeps < 40; ++sweeps) {
+    bool any = false;
+    for (int t = 0; t < D; t += 2) {
+      // even step: positions (2h, 2h+1) = (X, Y); afterwards Y moves down to the pair (2h-1, 2h) of half-warp h-1
+      any |= rotate(true);
+      store_col(bufE + hw * CS, Yw, Yv);
+      __syncthreads();
+      if (t == 0 && tid == 0) rotated[(sweeps + 1) & 1] = 0;
+      if (hw < 31) load_col(bufE + (hw + 1) * CS, Yw, Yv);
+      // odd step: positions (2h+1, 2h+2) = (X, Y) for h <= 30; half-warp 31 only keeps position 63 (its X)
+      any |= rotate(hw < 31);
+      if (hw < 31) store_col(bufO + (hw + 1) * CS, Xw, Xv);
+      __syncthreads();
+      // next even pair: first = what half-warp h-1 passed up (position 0 is the column parked in bufE[0]),
+      // second = this half-warp's Y (half-warp 31: the X it kept)
+      if (hw == 31) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { Yw[i] = Xw[i]; Yv[i] = Xv[i]; }
+      }
+      load_col(hw == 0 ? bufE : bufO + hw * CS, Xw, Xv);
+    }
+    if (any) rotated[sweeps & 1] = 1;
+    __syncthreads();
+    if (!rotated[sweeps & 1]) break;
+  }
+  __syncthreads();
+  store_col(S + (2 * hw) * CS, Xw, Xv);
+  store_col(S + (2 * hw + 1) * CS, Yw, Yv);
+  __syncthreads();
+  // |lambda_j| = ||W_j||; rank the columns and emit the k largest (descending), zero-padded to KP columns
+  {
+    const int warp = tid >> 5, nwarp = blockDim.x >> 5;
+    for (int c = warp; c < D; c += nwarp) {
+      double a = 0.0;
+      for (int r = lane; r < D; r += 32) a = fma(S[c * CS + r], S[c * CS + r], a);
+      a = warp_sum(a);
+      if (lane == 0) norms[c] = sqrt(a);
+    }
+  }
+  __syncthreads();
+  for (int idx = tid; idx < D * KP; idx += blockDim.x) {
+    const int c = idx % KP;
+    if (c >= k) { Vd[idx] = 0.0; Vf[idx] = 0.f; }
+  }
+  for (int c = tid; c < D; c += blockDim.x) {
+    int rank = 0;
+    const double nc = norms[c];
+    for (int o = 0; o < D; ++o) rank += (norms[o] > nc) || (norms[o] == nc && o < c);
+    if (rank < k) {
+      evals[rank] = nc;
+      for (int f = 0; f < D; ++f) {
+        const double v = S[c * CS + D + f];
+        Vd[(size_t)f * KP + rank] = v;
+        Vf[(size_t)f * KP + rank] = (float)v;
+      }
+    }
+  }
+  for (int idx = tid; idx < D * D; idx += blockDim.x) Vfull[idx] = S[(idx >> 6) * CS + D + (idx & 63)];
+  if (tid == 0) gate[3] = sweeps;
+}
+
+
 // d too large for one CTA's shared memory (d > 111): the same rotation scheme spread over several CTAs.  W and V live
 // in the workspace (1 MB at d = 256, L2 resident); every step the d/2 column pairs are rotated by one warp each
 // across the grid, and a cooperative grid barrier separates the steps.  Registers hold the two W and two V columns of
@@ -160,16 +334,15 @@ jacobi_topk_grid(const double* __restrict__ C, int d, int k, int KP, double* __r
     grid.sync();
     for (int idx = tid; idx < d * d; idx += nthr) {
       const int c = idx / d, r = idx - c * d;
-      const double* crow = C + (size_t)r * d;
       const double* vcol = V + (size_t)c * d;
       double acc = 0.0;
-      for (int g = 0; g < d; ++g) acc = fma(crow[g], vcol[g], acc);
+      for (int g = 0; g < d; ++g) acc = fma(C[(size_t)g * d + r], __ldcg(vcol + g), acc);  // C symmetric: coalesced
       W[idx] = acc;
     }
   } else {
     for (int idx = tid; idx < d * d; idx += nthr) {
       const int c = idx / d, r = idx - c * d;
-      W[idx] = C[(size_t)r * d + c];
+      W[idx] = C[idx];
       V[idx] = r == c ? 1.0 : 0.0;
     }
   }
@@ -222,7 +395,7 @@ jacobi_topk_grid(const double* __restrict__ C, int d, int k, int KP, double* __r
             __stcg(vq + r, sn * x + cs * y);
           }
         }
-        if (lane == 0) rot_flags[sweeps] = 1;
+        if (lane == 0 && ga * ga > kQuadCos2 * (al * be)) rot_flags[sweeps] = 1;
       }
       grid.sync();
     }
@@ -268,7 +441,11 @@ int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
   const int warm = (h->warm_batches % 256) != 0;  // periodic cold start keeps the accumulated basis orthonormal
   h->warm_batches++;
   if (h->profile) cudaEventRecord(h->ev[2], st);
-  if (need <= 200 * 1024) {
+  if (d == 64 && !h->force_generic) {
+    const size_t sm64 = (size_t)(64 * 128 + 64 * 64) * sizeof(double);  // columns (W | V) + the staged covariance
+    SB_CUDA(cudaFuncSetAttribute(jacobi64_regs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm64));
+    jacobi64_regs<<<1, 512, sm64, st>>>(h->d_C1, h->k, h->KP, h->d_V, h->d_Vf, h->d_evals, h->d_gate, h->d_Vfull, warm);
+  } else if (need <= 200 * 1024) {
     SB_CUDA(cudaFuncSetAttribute(jacobi_topk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     jacobi_topk<true><<<1, 1024, need, st>>>(h->d_C1, d, h->k, h->KP, nullptr, nullptr, h->d_V, h->d_Vf, h->d_evals,
                                             h->d_gate, h->d_Vfull, warm);

@@ -1,14 +1,15 @@
+"""Per-stage kernel times of one Mahalanobis batch of 2 Mi rows (usage: d256_stages.py [d ...]; ITERS=n batches)."""
 import sys, ctypes, torch
 sys.path.insert(0, '/root/repo')
 from seldon_core_b200 import OutlierMahalanobisB200, _cabi, synth
 dev = torch.device('cuda')
-for d in (128, 256):
+for d in [int(a) for a in sys.argv[1:]] or (128, 256):
     det = OutlierMahalanobisB200(n_components=16)
     det.set_option(_cabi.SB_OPT_PROFILE, 1)
     prime, _ = synth.maha_rows_torch(1 << 18, d, 16, 201, dev)
     X, _ = synth.maha_rows_torch(1 << 21, d, 16, 202, dev)
     det.score_device(prime)
-    for it in range(3):
+    for it in range(int(__import__('os').environ.get('ITERS', 3))):
         det.score_device(X)
         km = (ctypes.c_float * 5)()
         _cabi.check(_cabi.lib().sb_maha_kernel_times(det._h, km, torch.cuda.current_stream().cuda_stream))
