@@ -119,14 +119,26 @@ sub_scan_totals(const double* __restrict__ subproj, int nsub, int KQ, double* __
   }
 }
 
+// exclusive scan over the chunk totals, in place, starting from this rank's offset (one block, a thread per component)
 __global__ void __launch_bounds__(256)
-sub_scan_apply(double* __restrict__ subproj, int nsub, int KQ, const double* __restrict__ chunk_tot,
-               const double* __restrict__ rank_off) {
+sub_scan_chunks(double* __restrict__ chunk_tot, int nchunk, int KQ, const double* __restrict__ rank_off) {
+  for (int comp = threadIdx.x; comp < KQ; comp += blockDim.x) {
+    double run = rank_off[comp];
+#pragma unroll 8
+    for (int c = 0; c < nchunk; ++c) {
+      const double v = chunk_tot[(size_t)c * KQ + comp];
+      chunk_tot[(size_t)c * KQ + comp] = run;
+      run += v;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+sub_scan_apply(double* __restrict__ subproj, int nsub, int KQ, const double* __restrict__ chunk_pre) {
   const int chunk = blockIdx.x, nchunk = gridDim.x;
   const int s0 = chunk * kScanChunk, s1 = min(nsub, s0 + kScanChunk);
   for (int comp = threadIdx.x; comp < KQ; comp += blockDim.x) {
-    double run = rank_off[comp];
-    for (int c = 0; c < chunk; ++c) run += chunk_tot[(size_t)c * KQ + comp];
+    double run = chunk_pre[(size_t)chunk * KQ + comp];
     for (int s = s0; s < s1; ++s) {
       const double v = subproj[(size_t)s * KQ + comp];
       subproj[(size_t)s * KQ + comp] = run;
@@ -1444,7 +1456,7 @@ chain4(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t
 }
 
 // PC0 = V^T C0 V (KP x KP, zero padded), one block
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 project_cov(const double* __restrict__ C0, const double* __restrict__ V, int d, int KP, double* __restrict__ PC0) {
   extern __shared__ double T[];  // [d][KP] = C0 V
   for (int idx = threadIdx.x; idx < d * KP; idx += blockDim.x) {
@@ -1469,13 +1481,18 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
   const size_t PS = (size_t)d + (size_t)d * d;
   if (h->profile) cudaEventRecord(h->ev[4], st);
   SB_CUDA(cudaFuncSetAttribute(project_cov, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxD * kMaxKP * 8));
-  project_cov<<<1, 256, (size_t)d * KP * sizeof(double), st>>>(h->d_C, h->d_V, d, KP, h->d_PC0);
+  project_cov<<<1, 1024, (size_t)d * KP * sizeof(double), st>>>(h->d_C, h->d_V, d, KP, h->d_PC0);
   SB_LAUNCH_CHECK();
   int grid = nsub < kNumSMs * 8 ? nsub : kNumSMs * 8;
   const int FC = d < 8192 / d ? d : 8192 / d;
   const size_t sp_smem = ((((size_t)FC * d + 3) & ~(size_t)3) + (size_t)FC * KP) * sizeof(float);
-  sub_project<double><<<1, 256, sp_smem, st>>>(ws.rank_pre + 1, PS, 1, d, KP, h->d_Vf, rank_proj);
-  SB_LAUNCH_CHECK();
+  if (h->row0 == 0) {
+    // no rows before this shard (single GPU, or rank 0): the offset of every prefix is zero
+    SB_CUDA(cudaMemsetAsync(rank_proj, 0, (size_t)KQ * sizeof(double), st));
+  } else {
+    sub_project<double><<<1, 256, sp_smem, st>>>(ws.rank_pre + 1, PS, 1, d, KP, h->d_Vf, rank_proj);
+    SB_LAUNCH_CHECK();
+  }
   if (h->split_pass2) {
     // the projection kernel of pass 2 produces the per-sub-segment statistics; scan and start inverses follow it
     if (h->profile) cudaEventRecord(h->ev[5], st);
@@ -1486,7 +1503,9 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
   const int nchunk = (int)ceil_div(nsub, kScanChunk);
   sub_scan_totals<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
   SB_LAUNCH_CHECK();
-  sub_scan_apply<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot, rank_proj);
+  sub_scan_chunks<<<1, 256, 0, st>>>(ws.chunk_tot, nchunk, KQ, rank_proj);
+  SB_LAUNCH_CHECK();
+  sub_scan_apply<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
   SB_LAUNCH_CHECK();
   sub_start<KP><<<(int)ceil_div(nsub, 4), 128, 0, st>>>(ws.subproj, h->d_PC0, h->lay, h->k, (long long)h->n_eff,
                                                        (long long)h->row0, ws.sub_P, ws.sub_Z, ws.sub_flags);
@@ -1532,7 +1551,9 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
     const int nchunk = (int)ceil_div(nsub, kScanChunk);
     sub_scan_totals<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
     SB_LAUNCH_CHECK();
-    sub_scan_apply<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot, ws.rank_proj);
+    sub_scan_chunks<<<1, 256, 0, st>>>(ws.chunk_tot, nchunk, KQ, ws.rank_proj);
+    SB_LAUNCH_CHECK();
+    sub_scan_apply<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
     SB_LAUNCH_CHECK();
     sub_start<KP><<<(int)ceil_div(nsub, 4), 128, 0, st>>>(ws.subproj, h->d_PC0, L, h->k, (long long)h->n_eff,
                                                          (long long)h->row0, ws.sub_P, ws.sub_Z, ws.sub_flags);
