@@ -21,9 +21,14 @@
 //     d = 256: two accumulators (rows 0-127 x 256 columns, rows 128-255 x columns 128-255: the block below the
 //              diagonal is mirrored on store), 384 of the 512 TMEM columns, six MMAs per 8 rows.
 //
-// Bounds (B200, measured, 16Mi rows): d = 64: 1.07 ms = 4.0 TB/s, 61 % of the measured HBM copy rate; the producers'
-// issue rate (about 270 instructions per thread and 128-row chunk) is the limiter.  d = 128: 2.7 TB/s, tensor pipe and
-// HBM about level.  d = 256: 2.1 TB/s, tensor pipe (2*d*d*0.75*3 flop per row).
+// d = 64 additionally stages the raw rows in shared memory: a loader warp issues one cp.async.bulk per 32 KB chunk
+// into a 3-slot ring (mbarrier complete_tx), the producers read their float4 from there; the tile ring has two slots.
+//
+// Bounds (B200, measured, 16Mi rows): d = 64: 1.01 ms = 4.2 TB/s, 65 % of the measured HBM copy rate.  Shared-memory
+// bandwidth is the limiter: per 32 KB chunk 32 KB bulk-copy writes + 32 KB raw reads + 64 KB tile writes + 96 KB
+// operand reads by the MMAs = 224 KB at 128 B/clk = 1750 clk against 1424 clk of HBM time (without the raw staging the
+// kernel moved 160 KB per chunk but stalled on HBM latency: 1.07 ms).  d = 128: 2.7 TB/s, tensor pipe and HBM about
+// level.  d = 256: 2.1 TB/s, tensor pipe (2*d*d*0.75*3 flop per row).
 #include "maha.cuh"
 
 namespace sb {
@@ -84,19 +89,26 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
       : "memory");
 }
 
-constexpr int kUmmaStages = 3;
+// d = 64 is HBM-latency bound: its rows are staged raw in shared memory by bulk copies (cp.async.bulk, a loader warp;
+// three 32 KB slots in flight per SM cost no registers) and the tile ring gives up one slot for that.
+__host__ __device__ constexpr bool umma_raw_staged(int D) { return D == 64; }
+__host__ __device__ constexpr int umma_tile_stages(int D) { return umma_raw_staged(D) ? 2 : 3; }
+constexpr int kRawStages = 3;
 // rows per chunk: 8192 / D, so every tile is 32 KB and every thread converts four float4 per chunk
 __host__ __device__ constexpr int umma_chunk_rows(int D) { return 8192 / D; }
 
 __host__ __device__ constexpr size_t umma_smem_bytes(int D, int terms) {
-  return (size_t)kUmmaStages * (terms == 3 ? 2 : 1) * umma_chunk_rows(D) * D * 4 + (size_t)3 * D * 4 + 1024 /* alignment slack */;
+  return (size_t)umma_tile_stages(D) * (terms == 3 ? 2 : 1) * umma_chunk_rows(D) * D * 4 +
+         (umma_raw_staged(D) ? (size_t)kRawStages * umma_chunk_rows(D) * D * 4 : 0) +
+         (D > 128 ? (size_t)3 * D * 4 : 0) /* mean and clip bounds when they do not fit in registers */ + 1024 /* alignment slack */;
 }
 
 constexpr int kUmmaThreads = 512;            // producer threads (16 warps); one more warp issues the MMAs
 constexpr int kUmmaBlock = kUmmaThreads + 32;
+__host__ __device__ constexpr int umma_block(int D) { return kUmmaBlock + (umma_raw_staged(D) ? 32 : 0); }  // + loader warp
 
 template <int D, bool CLIP, int TERMS>
-__global__ void __launch_bounds__(kUmmaBlock, 1)
+__global__ void __launch_bounds__(umma_block(D), 1)
 pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const float* __restrict__ mean_f,
                 const float* __restrict__ lo_f, const float* __restrict__ hi_f, float* __restrict__ partials) {
   constexpr int PS = D + D * D;
@@ -109,7 +121,9 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   // (d = 128 with two accumulators HH, LH was measured slower than the plain three products: the longer epilogue is not
   // hidden behind the MMAs of a 900-row sub-segment.)
   constexpr bool STACK = D == 64 && TERMS == 3;
-  constexpr bool PF2 = D == 64;  // prefetch distance 2 (d = 64 is HBM-latency bound; the wider shapes are tensor bound)
+  constexpr bool RAW = umma_raw_staged(D);
+  constexpr int kUmmaStages = umma_tile_stages(D);
+  constexpr int RAWBYTES = umma_chunk_rows(D) * D * 4;
   constexpr uint32_t SBO = (STACK ? 2 : 1) * NSLAB * 512;  // between 4-row groups
   constexpr int kChunkRows = umma_chunk_rows(D);
   constexpr int NROW = kChunkRows / 32;         // rows per thread and chunk: (tid >> 4) + 32*j
@@ -120,11 +134,14 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   constexpr int TMEM_COLS = D == 256 ? 512 : D;  // power of two >= columns used (D = 256 uses 384)
   extern __shared__ uint8_t umma_smem_raw[];
   uint8_t* tiles = (uint8_t*)(((uintptr_t)umma_smem_raw + 1023) & ~(uintptr_t)1023);
-  float* ms = reinterpret_cast<float*>(tiles + kUmmaStages * NT * TILE);
+  uint8_t* raw = tiles + kUmmaStages * NT * TILE;  // [kRawStages][chunk rows][D] fp32, row major (RAW only)
+  float* ms = reinterpret_cast<float*>(raw + (RAW ? kRawStages * RAWBYTES : 0));
   float* los = ms + D;
   float* his = los + D;
   __shared__ uint64_t bar_full[kUmmaStages];   // 16 producer warps have filled the slot
   __shared__ uint64_t bar_empty[kUmmaStages];  // the MMAs reading the slot have completed (tcgen05.commit)
+  __shared__ uint64_t bar_rfull[kRawStages];   // the bulk copy of a raw chunk has landed
+  __shared__ uint64_t bar_rempty[kRawStages];  // 16 producer warps have converted the raw chunk
   __shared__ uint64_t bar_acc;                 // all MMAs of the sub-segment have completed
   __shared__ uint64_t bar_tfree;               // 16 producer warps have drained the accumulator
   __shared__ uint32_t tmem_base_s;
@@ -132,15 +149,22 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int krow = tid >> 4, piece0 = tid & 15;  // a warp instruction reads 256 contiguous bytes of each of 2 rows
-  for (int f = tid; f < D; f += kUmmaBlock) {
-    ms[f] = mean_f[f];
-    los[f] = CLIP ? lo_f[f] : 0.f;
-    his[f] = CLIP ? hi_f[f] : 0.f;
+  constexpr bool HOIST = NPIECE <= 2;  // this thread's mean / clip bounds stay in registers (no shared copy)
+  if (!HOIST) {
+    for (int f = tid; f < D; f += umma_block(D)) {
+      ms[f] = mean_f[f];
+      los[f] = CLIP ? lo_f[f] : 0.f;
+      his[f] = CLIP ? hi_f[f] : 0.f;
+    }
   }
   if (tid == 0) {
     for (int s = 0; s < kUmmaStages; ++s) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 16;" ::"r"(smem_u32(&bar_full[s])));
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar_empty[s])));
+    }
+    for (int s = 0; s < kRawStages; ++s) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar_rfull[s])));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 16;" ::"r"(smem_u32(&bar_rempty[s])));
     }
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar_acc)));
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 16;" ::"r"(smem_u32(&bar_tfree)));
@@ -156,7 +180,33 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   const uint32_t tmem = tmem_base_s;
   const uint32_t tiles_u32 = smem_u32(tiles);
 
-  if (warp == kUmmaThreads / 32) {
+  if (RAW && warp == kUmmaThreads / 32 + 1) {
+    // ===== loader warp: one lane walks the (sub-segment, chunk) sequence and keeps the raw ring full
+    if (lane == 0) {
+      uint32_t itl = 0;
+      for (int sub = blockIdx.x; sub < lay.nsub; sub += gridDim.x) {
+        const int64_t r0 = sub_begin(lay, sub), r1 = sub_begin(lay, sub + 1);
+        const int nchunks = (int)((r1 - r0 + kChunkRows - 1) / kChunkRows);
+        for (int c = 0; c < nchunks; ++c, ++itl) {
+          const uint32_t slot = itl % kRawStages;
+          if (itl >= (uint32_t)kRawStages) mbar_wait(smem_u32(&bar_rempty[slot]), ((itl / kRawStages) - 1) & 1);
+          const int64_t row = r0 + (int64_t)c * kChunkRows;
+          const int nrows = (int)(r1 - row < kChunkRows ? r1 - row : kChunkRows);
+          const uint32_t bar = smem_u32(&bar_rfull[slot]);
+          const uint32_t dst = smem_u32(raw + slot * RAWBYTES);
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(nrows * D * 4)) : "memory");
+          if (ld == D) {
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dst), "l"(X + row * ld), "r"((uint32_t)(nrows * D * 4)), "r"(bar) : "memory");
+          } else {
+            for (int k = 0; k < nrows; ++k)
+              asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                           ::"r"(dst + (uint32_t)(k * D * 4)), "l"(X + (row + k) * ld), "r"((uint32_t)(D * 4)), "r"(bar) : "memory");
+          }
+        }
+      }
+    }
+  } else if (warp == kUmmaThreads / 32) {
     // ===== MMA warp: one lane issues; walks the same (sub-segment, chunk) sequence as the producers
     if (lane == 0) {
       uint32_t itm = 0, tfree_parity = 0;
@@ -225,14 +275,14 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   const uint32_t b0 = 16u * (piece0 & 7);
   const uint32_t off0 = (uint32_t)(krow >> 2) * SBO + (uint32_t)(piece0 >> 3) * LBO + (uint32_t)(krow & 3) * 128u +
                         ((((b0 >> 5) ^ (uint32_t)(krow & 3)) << 5) | (b0 & 31u));
-  constexpr bool HOIST = NPIECE <= 2;  // keep this thread's mean / clip bounds in registers
   float4 m_r[HOIST ? NPIECE : 1], l_r[HOIST ? NPIECE : 1], h_r[HOIST ? NPIECE : 1];
   if (HOIST) {
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < NPIECE; ++i) {
-      m_r[i] = *reinterpret_cast<const float4*>(ms + 4 * (piece0 + 16 * i));
-      l_r[i] = *reinterpret_cast<const float4*>(los + 4 * (piece0 + 16 * i));
-      h_r[i] = *reinterpret_cast<const float4*>(his + 4 * (piece0 + 16 * i));
+      m_r[i] = *reinterpret_cast<const float4*>(mean_f + 4 * (piece0 + 16 * i));
+      l_r[i] = CLIP ? *reinterpret_cast<const float4*>(lo_f + 4 * (piece0 + 16 * i)) : zero4;
+      h_r[i] = CLIP ? *reinterpret_cast<const float4*>(hi_f + 4 * (piece0 + 16 * i)) : zero4;
     }
   }
   uint32_t acc_parity = 0;
@@ -305,23 +355,21 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
       ++it;
     };
 
-    if (PF2) {
-      // two chunks (64 KB per SM) stay in flight ahead of the one being converted: one does not cover the HBM latency at
-      // full rate (148 SMs x 32 KB / ~1.5 us = 3 TB/s).  Three named buffers, rotated by unrolling (no register moves).
-      float4 bufA[NROW][NPIECE], bufB[NROW][NPIECE], bufC[NROW][NPIECE];
-      if (nchunks > 0) load_chunk(0, bufA);
-      if (nchunks > 1) load_chunk(1, bufB);
-      for (int c = 0; c < nchunks; c += 3) {
-        if (c + 2 < nchunks) load_chunk(c + 2, bufC);
-        convert_chunk(c, bufA);
-        if (c + 1 < nchunks) {
-          if (c + 3 < nchunks) load_chunk(c + 3, bufA);
-          convert_chunk(c + 1, bufB);
-        }
-        if (c + 2 < nchunks) {
-          if (c + 4 < nchunks) load_chunk(c + 4, bufB);
-          convert_chunk(c + 2, bufC);
-        }
+    if (RAW) {
+      // rows arrive in shared memory by bulk copy; this thread's float4 of row k sits at raw[k][4 piece0 ..]: a warp
+      // reads 2 x 256 contiguous bytes, conflict free
+      for (int c = 0; c < nchunks; ++c) {
+        const uint32_t slot = it % kRawStages;
+        mbar_wait(smem_u32(&bar_rfull[slot]), (it / kRawStages) & 1);
+        float4 buf[NROW][NPIECE];
+        const float4* rp = reinterpret_cast<const float4*>(raw + slot * RAWBYTES);
+#pragma unroll
+        for (int j = 0; j < NROW; ++j)
+#pragma unroll
+          for (int i = 0; i < NPIECE; ++i) buf[j][i] = rp[(krow + 32 * j) * (D / 4) + piece0 + 16 * i];
+        convert_chunk(c, buf);
+        __syncwarp();
+        if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&bar_rempty[slot])) : "memory");
       }
     } else {
       float4 bufA[NROW][NPIECE], bufB[NROW][NPIECE];
@@ -458,7 +506,7 @@ int launch_umma_d(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws
   do {                                                                                                                  \
     const size_t smem = umma_smem_bytes(D, TERMSV);                                                                     \
     SB_CUDA(cudaFuncSetAttribute(pass1_gram_umma<D, CLIPV, TERMSV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    pass1_gram_umma<D, CLIPV, TERMSV><<<grid, kUmmaBlock, smem, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials); \
+    pass1_gram_umma<D, CLIPV, TERMSV><<<grid, umma_block(D), smem, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials); \
   } while (0)
   if (h->use_clip) {
     if (h->gram_terms == 3) SB_UMMA_LAUNCH(true, 3); else SB_UMMA_LAUNCH(true, 1);
