@@ -48,17 +48,27 @@ unpack_tensor_kernel(const uint8_t* __restrict__ vals, int64_t rows, int64_t col
   const int64_t total = rows * cols;
   const uint8_t* end = vals + 8 * total;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    double v;
-    if (aligned) {
-      v = __ldcs(reinterpret_cast<const double*>(vals) + i);
-    } else {
-      v = __longlong_as_double((long long)load_u64_unaligned(vals + 8 * i, end));
+  constexpr int U = 4;  // independent loads in flight per thread, each warp access stays contiguous
+  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < total; i0 += U * stride) {
+    double v[U];
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const int64_t i = i0 + j * stride;
+      v[j] = 0.0;
+      if (i < total)
+        v[j] = aligned ? __ldcs(reinterpret_cast<const double*>(vals) + i)
+                       : __longlong_as_double((long long)load_u64_unaligned(vals + 8 * i, end));
     }
-    int64_t r = i, c = 0;
-    if (ld != cols || STD) { r = i / cols; c = i - r * cols; }
-    if (STD) v = (v - (double)__ldg(mu + c)) * (double)__ldg(inv_sigma + c);
-    if (ld != cols) out[r * ld + c] = (float)v; else out[i] = (float)v;
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const int64_t i = i0 + j * stride;
+      if (i >= total) break;
+      int64_t r = i, c = 0;
+      if (ld != cols || STD) { r = i / cols; c = i - r * cols; }
+      double w = v[j];
+      if (STD) w = (w - (double)__ldg(mu + c)) * (double)__ldg(inv_sigma + c);
+      if (ld != cols) out[r * ld + c] = (float)w; else __stcs(out + i, (float)w);
+    }
   }
 }
 
@@ -97,14 +107,26 @@ template <typename TIn>
 __global__ void __launch_bounds__(256)
 pack_tensor_kernel(const TIn* __restrict__ in, int64_t n, uint8_t* __restrict__ out, int aligned) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const double v = (double)in[i];
-    if (aligned) {
-      __stcs(reinterpret_cast<double*>(out) + i, v);
-    } else {
-      uint64_t b = (uint64_t)__double_as_longlong(v);
+  constexpr int U = 4;
+  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += U * stride) {
+    TIn x[U];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) out[8 * i + k] = (uint8_t)(b >> (8 * k));
+    for (int j = 0; j < U; ++j) {
+      const int64_t i = i0 + j * stride;
+      x[j] = i < n ? __ldcs(in + i) : TIn(0);
+    }
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      const int64_t i = i0 + j * stride;
+      if (i >= n) break;
+      const double v = (double)x[j];
+      if (aligned) {
+        __stcs(reinterpret_cast<double*>(out) + i, v);
+      } else {
+        uint64_t b = (uint64_t)__double_as_longlong(v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) out[8 * i + k] = (uint8_t)(b >> (8 * k));
+      }
     }
   }
 }
@@ -245,6 +267,57 @@ pack_listvalue_staged(const TIn* __restrict__ in, int64_t rows, int cols, int ro
 }
 
 // ---- cols % 4 == 0: four consecutive records (44 bytes = 11 words) per thread, no division, no per-byte work ----
+// the parse of one staged chunk of nr rows (cols % 4 == 0): returns nonzero if a tag or row header is wrong
+__device__ __forceinline__ int unpack4_chunk(const uint32_t* sm_words, int nr, int q, int row_bytes, int hdr, uint32_t l1,
+                                             uint32_t l2, float* __restrict__ out, int64_t r0, int64_t ld, bool vec_out) {
+  int bad = 0;
+  // (row, run) pairs: consecutive threads take consecutive runs of a row
+  const int total = nr * q;
+  int r = threadIdx.x / q, u = threadIdx.x - r * q;
+  const int dr = blockDim.x / q, du = blockDim.x - dr * q;
+  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    const int o = r * row_bytes + hdr + 44 * u;  // byte offset of the first of 4 records
+    const int k = o >> 2, sh = (o & 3) * 8;
+    uint32_t w[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) w[i] = sm_words[k + i];
+    uint32_t a[11];  // the 44 bytes, word aligned
+#pragma unroll
+    for (int i = 0; i < 11; ++i) a[i] = __funnelshift_r(w[i], w[i + 1], sh);
+    float v[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      // record e occupies bytes 11e .. 11e+10 of a[]: tag at 11e, value at 11e+3
+      const int tb = 11 * e, vb = tb + 3;
+      const uint32_t tag = __funnelshift_r(a[tb >> 2], a[(tb >> 2) + 1 < 11 ? (tb >> 2) + 1 : 10], (tb & 3) * 8) & 0xffffffu;
+      const uint32_t lo = __funnelshift_r(a[vb >> 2], a[(vb >> 2) + 1], (vb & 3) * 8);
+      const uint32_t hi = (vb >> 2) + 2 < 11 ? __funnelshift_r(a[(vb >> 2) + 1], a[(vb >> 2) + 2], (vb & 3) * 8)
+                                             : (a[(vb >> 2) + 1] >> ((vb & 3) * 8));
+      if (tag != 0x11090au) bad = 1;
+      v[e] = (float)__hiloint2double((int)hi, (int)lo);
+    }
+    float* dst = out + (r0 + r) * ld + 4 * u;
+    if (vec_out) *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+    else { dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2]; dst[3] = v[3]; }
+    if (u == 0) {
+      const uint8_t* h = reinterpret_cast<const uint8_t*>(sm_words) + r * row_bytes;
+      int pos = 0;
+      if (h[pos++] != 0x0a) bad = 1;
+      uint32_t vv = 0; int shf = 0;
+      while (pos < hdr) { const uint8_t b = h[pos++]; vv |= (uint32_t)(b & 0x7f) << shf; shf += 7; if (!(b & 0x80)) break; }
+      if (vv != l1) bad = 1;
+      if (pos < hdr && h[pos++] != 0x32) bad = 1;
+      vv = 0; shf = 0;
+      while (pos < hdr) { const uint8_t b = h[pos++]; vv |= (uint32_t)(b & 0x7f) << shf; shf += 7; if (!(b & 0x80)) break; }
+      if (vv != l2 || pos != hdr) bad = 1;
+    }
+    r += dr; u += du;
+    if (u >= q) { u -= q; ++r; }
+  }
+  return bad;
+}
+
+
 __global__ void __launch_bounds__(256)
 unpack_listvalue_staged4(const uint8_t* __restrict__ wire, int64_t rows, int cols, int row_bytes, int hdr, uint32_t l1,
                          uint32_t l2, int R, float* __restrict__ out, int64_t ld, int32_t* __restrict__ status) {
@@ -265,52 +338,31 @@ unpack_listvalue_staged4(const uint8_t* __restrict__ wire, int64_t rows, int col
     for (int b = (nvec << 4) + threadIdx.x; b < nbytes; b += blockDim.x)
       reinterpret_cast<uint8_t*>(sm_words)[b] = src[b];
     __syncthreads();
-    // (row, run) pairs: consecutive threads take consecutive runs of a row
-    const int total = nr * q;
-    int r = threadIdx.x / q, u = threadIdx.x - r * q;
-    const int dr = blockDim.x / q, du = blockDim.x - dr * q;
-    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-      const int o = r * row_bytes + hdr + 44 * u;  // byte offset of the first of 4 records
-      const int k = o >> 2, sh = (o & 3) * 8;
-      uint32_t w[12];
-#pragma unroll
-      for (int i = 0; i < 12; ++i) w[i] = sm_words[k + i];
-      uint32_t a[11];  // the 44 bytes, word aligned
-#pragma unroll
-      for (int i = 0; i < 11; ++i) a[i] = __funnelshift_r(w[i], w[i + 1], sh);
-      float v[4];
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        // record e occupies bytes 11e .. 11e+10 of a[]: tag at 11e, value at 11e+3
-        const int tb = 11 * e, vb = tb + 3;
-        const uint32_t tag = __funnelshift_r(a[tb >> 2], a[(tb >> 2) + 1 < 11 ? (tb >> 2) + 1 : 10], (tb & 3) * 8) & 0xffffffu;
-        const uint32_t lo = __funnelshift_r(a[vb >> 2], a[(vb >> 2) + 1], (vb & 3) * 8);
-        const uint32_t hi = (vb >> 2) + 2 < 11 ? __funnelshift_r(a[(vb >> 2) + 1], a[(vb >> 2) + 2], (vb & 3) * 8)
-                                               : (a[(vb >> 2) + 1] >> ((vb & 3) * 8));
-        if (tag != 0x11090au) bad = 1;
-        v[e] = (float)__hiloint2double((int)hi, (int)lo);
-      }
-      float* dst = out + (r0 + r) * ld + 4 * u;
-      if (vec_out) *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
-      else { dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2]; dst[3] = v[3]; }
-      if (u == 0) {
-        const uint8_t* h = reinterpret_cast<const uint8_t*>(sm_words) + r * row_bytes;
-        int pos = 0;
-        if (h[pos++] != 0x0a) bad = 1;
-        uint32_t vv = 0; int shf = 0;
-        while (pos < hdr) { const uint8_t b = h[pos++]; vv |= (uint32_t)(b & 0x7f) << shf; shf += 7; if (!(b & 0x80)) break; }
-        if (vv != l1) bad = 1;
-        if (pos < hdr && h[pos++] != 0x32) bad = 1;
-        vv = 0; shf = 0;
-        while (pos < hdr) { const uint8_t b = h[pos++]; vv |= (uint32_t)(b & 0x7f) << shf; shf += 7; if (!(b & 0x80)) break; }
-        if (vv != l2 || pos != hdr) bad = 1;
-      }
-      r += dr; u += du;
-      if (u >= q) { u -= q; ++r; }
-    }
+    bad |= unpack4_chunk(sm_words, nr, q, row_bytes, hdr, l1, l2, out, r0, ld, vec_out);
   }
   if (bad) atomicExch(status, 1);
 }
+
+template <typename TIn>
+struct Vec4 { TIn v[4]; };
+// four consecutive inputs (16-byte aligned: cols % 4 == 0 and an aligned base, else element loads)
+template <typename TIn>
+__device__ __forceinline__ Vec4<TIn> load4(const TIn* src, bool aligned) {
+  Vec4<TIn> o;
+  if (aligned) {
+    const uint4 w = __ldcs(reinterpret_cast<const uint4*>(src));
+    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) memcpy(&o.v[e], &ww[e], 4);
+  } else {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) o.v[e] = src[e];
+  }
+  return o;
+}
+template <typename TIn>
+__device__ __forceinline__ void pack4_chunk(uint32_t* sm_words, const TIn* __restrict__ in, int64_t r0, int nr, int cols,
+                                            int q, int row_bytes, int hdr, uint32_t l1, uint32_t l2);
 
 template <typename TIn>
 __global__ void __launch_bounds__(256)
@@ -329,60 +381,7 @@ pack_listvalue_staged4(const TIn* __restrict__ in, int64_t rows, int cols, int r
     for (int v = threadIdx.x; v < ((nbytes + 15) >> 4) + 1; v += blockDim.x)
       reinterpret_cast<uint4*>(sm_words)[v] = make_uint4(0u, 0u, 0u, 0u);
     __syncthreads();
-    const int total = nr * q;
-    int r = threadIdx.x / q, u = threadIdx.x - r * q;
-    const int dr = blockDim.x / q, du = blockDim.x - dr * q;
-    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-      const TIn* src = in + (r0 + r) * (int64_t)cols + 4 * u;
-      uint32_t a[12];  // 44 bytes of four records + one spill word
-      a[11] = 0;
-      uint32_t lo[4], hi[4];
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const double dv = (double)src[e];
-        lo[e] = (uint32_t)__double2loint(dv);
-        hi[e] = (uint32_t)__double2hiint(dv);
-      }
-      // bytes: [0a 09 11 v0..v7] x 4, little endian words
-      a[0] = 0x0011090au | (lo[0] << 24);
-      a[1] = (lo[0] >> 8) | (hi[0] << 24);
-      a[2] = (hi[0] >> 8) | 0x0a000000u;
-      a[3] = 0x00001109u | (lo[1] << 16);
-      a[4] = (lo[1] >> 16) | (hi[1] << 16);
-      a[5] = (hi[1] >> 16) | 0x090a0000u;
-      a[6] = 0x00000011u | (lo[2] << 8);
-      a[7] = (lo[2] >> 24) | (hi[2] << 8);
-      a[8] = (hi[2] >> 24) | 0x11090a00u;
-      a[9] = lo[3];
-      a[10] = hi[3];
-      const int o = r * row_bytes + hdr + 44 * u;
-      const int k = o >> 2, sh = (o & 3) * 8;
-      if (sh == 0) {
-#pragma unroll
-        for (int i = 0; i < 11; ++i) sm_words[k + i] = a[i];
-      } else {
-        atomicOr(sm_words + k, a[0] << sh);  // first and last words are shared with the neighbouring runs / header
-#pragma unroll
-        for (int i = 1; i < 11; ++i) sm_words[k + i] = __funnelshift_l(a[i - 1], a[i], sh);
-        atomicOr(sm_words + k + 11, a[10] >> (32 - sh));
-      }
-      if (u == 0) {
-        uint8_t hb[12];
-        int pos = 0;
-        hb[pos++] = 0x0a;
-        uint32_t v = l1;
-        while (v >= 0x80) { hb[pos++] = (uint8_t)(v | 0x80); v >>= 7; }
-        hb[pos++] = (uint8_t)v;
-        hb[pos++] = 0x32;
-        v = l2;
-        while (v >= 0x80) { hb[pos++] = (uint8_t)(v | 0x80); v >>= 7; }
-        hb[pos++] = (uint8_t)v;
-        const int ob = r * row_bytes;
-        for (int b = 0; b < pos; ++b) atomicOr(sm_words + ((ob + b) >> 2), (uint32_t)hb[b] << (((ob + b) & 3) * 8));
-      }
-      r += dr; u += du;
-      if (u >= q) { u -= q; ++r; }
-    }
+    pack4_chunk(sm_words, in, r0, nr, cols, q, row_bytes, hdr, l1, l2);
     __syncthreads();
     uint8_t* dst = out + r0 * (int64_t)row_bytes;
     const int nvec = nbytes >> 4;
@@ -390,6 +389,169 @@ pack_listvalue_staged4(const TIn* __restrict__ in, int64_t rows, int cols, int r
       __stcs(reinterpret_cast<uint4*>(dst) + v, reinterpret_cast<const uint4*>(sm_words)[v]);
     for (int b = (nvec << 4) + threadIdx.x; b < nbytes; b += blockDim.x) dst[b] = reinterpret_cast<const uint8_t*>(sm_words)[b];
   }
+}
+
+// ---- ring-buffered variants: the chunk moves between global and shared memory by bulk copies (cp.async.bulk), so a
+// CTA has up to kLvStages - 1 chunks in flight while it parses / assembles another.
+constexpr int kLvStages = 4;
+// two slots: a third one (or fetching the inputs a chunk ahead) costs resident CTAs and was measured slower
+constexpr int kLvPackSlots = 2;
+
+__device__ __forceinline__ void lv_mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done)
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+}
+
+__global__ void __launch_bounds__(256)
+unpack_listvalue_ring4(const uint8_t* __restrict__ wire, int64_t rows, int cols, int row_bytes, int hdr, uint32_t l1,
+                       uint32_t l2, int R, int slot_bytes, float* __restrict__ out, int64_t ld,
+                       int32_t* __restrict__ status) {
+  extern __shared__ __align__(128) uint8_t lv_ring[];  // [kLvStages][slot_bytes]
+  __shared__ uint64_t full[kLvStages];
+  const int64_t nchunks = (rows + R - 1) / R;
+  const int q = cols >> 2;
+  const bool vec_out = (ld & 3) == 0 && (((uintptr_t)out) & 15) == 0;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kLvStages; ++s)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&full[s])));
+    asm volatile("fence.mbarrier_init.release.cluster;");
+  }
+  __syncthreads();
+  // this CTA's chunks: blockIdx.x + j * gridDim.x
+  const int64_t mine = blockIdx.x < nchunks ? (nchunks - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+  auto issue = [&](int64_t j) {  // thread 0 only
+    const int64_t ch = blockIdx.x + j * (int64_t)gridDim.x;
+    const int64_t r0 = ch * R;
+    const int nr = (int)min((int64_t)R, rows - r0);
+    const uint32_t bytes = (uint32_t)(nr * row_bytes) & ~15u;  // the last chunk's tail (< 16 B) is read directly
+    const uint32_t slot = (uint32_t)(j % kLvStages);
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&full[slot]);
+    const uint32_t dst = (uint32_t)__cvta_generic_to_shared(lv_ring + (size_t)slot * slot_bytes);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier generic reads of the slot are done
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    if (bytes)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(dst), "l"(wire + r0 * (int64_t)row_bytes), "r"(bytes), "r"(bar) : "memory");
+  };
+  if (threadIdx.x == 0)
+    for (int64_t j = 0; j < kLvStages - 1 && j < mine; ++j) issue(j);
+  int bad = 0;
+  for (int64_t i = 0; i < mine; ++i) {
+    // every thread has passed the barrier that ended iteration i - 1, so the slot of chunk i - 1 is free again
+    if (threadIdx.x == 0 && i + kLvStages - 1 < mine) issue(i + kLvStages - 1);
+    const int64_t ch = blockIdx.x + i * (int64_t)gridDim.x;
+    const int64_t r0 = ch * R;
+    const int nr = (int)min((int64_t)R, rows - r0);
+    const int nbytes = nr * row_bytes;
+    uint8_t* slot = lv_ring + (size_t)(i % kLvStages) * slot_bytes;
+    lv_mbar_wait((uint32_t)__cvta_generic_to_shared(&full[i % kLvStages]), (uint32_t)((i / kLvStages) & 1));
+    if ((nbytes & 15) != 0) {  // last chunk only
+      const uint8_t* src = wire + r0 * (int64_t)row_bytes;
+      for (int b = (nbytes & ~15) + threadIdx.x; b < nbytes; b += blockDim.x) slot[b] = src[b];
+      __syncthreads();
+    }
+    bad |= unpack4_chunk(reinterpret_cast<const uint32_t*>(slot), nr, q, row_bytes, hdr, l1, l2, out, r0, ld, vec_out);
+    __syncthreads();
+  }
+  if (bad) atomicExch(status, 1);
+}
+
+// the assembly of one chunk of nr rows in shared memory (cols % 4 == 0); the slot must have been zeroed
+template <typename TIn>
+__device__ __forceinline__ void pack4_chunk(uint32_t* sm_words, const TIn* __restrict__ in, int64_t r0, int nr, int cols,
+                                            int q, int row_bytes, int hdr, uint32_t l1, uint32_t l2) {
+  const bool aligned = (((uintptr_t)in) & 15) == 0;
+  const int total = nr * q;
+  int r = threadIdx.x / q, u = threadIdx.x - r * q;
+  const int dr = blockDim.x / q, du = blockDim.x - dr * q;
+  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    const TIn* src = in + (r0 + r) * (int64_t)cols + 4 * u;
+    const Vec4<TIn> x = load4(src, aligned);
+    uint32_t a[11];
+    uint32_t lo[4], hi[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const double dv = (double)x.v[e];
+      lo[e] = (uint32_t)__double2loint(dv);
+      hi[e] = (uint32_t)__double2hiint(dv);
+    }
+    // bytes: [0a 09 11 v0..v7] x 4, little endian words
+    a[0] = 0x0011090au | (lo[0] << 24);
+    a[1] = (lo[0] >> 8) | (hi[0] << 24);
+    a[2] = (hi[0] >> 8) | 0x0a000000u;
+    a[3] = 0x00001109u | (lo[1] << 16);
+    a[4] = (lo[1] >> 16) | (hi[1] << 16);
+    a[5] = (hi[1] >> 16) | 0x090a0000u;
+    a[6] = 0x00000011u | (lo[2] << 8);
+    a[7] = (lo[2] >> 24) | (hi[2] << 8);
+    a[8] = (hi[2] >> 24) | 0x11090a00u;
+    a[9] = lo[3];
+    a[10] = hi[3];
+    const int o = r * row_bytes + hdr + 44 * u;
+    const int k = o >> 2, sh = (o & 3) * 8;
+    if (sh == 0) {
+#pragma unroll
+      for (int i = 0; i < 11; ++i) sm_words[k + i] = a[i];
+    } else {
+      atomicOr(sm_words + k, a[0] << sh);  // first and last words are shared with the neighbouring runs / header
+#pragma unroll
+      for (int i = 1; i < 11; ++i) sm_words[k + i] = __funnelshift_l(a[i - 1], a[i], sh);
+      atomicOr(sm_words + k + 11, a[10] >> (32 - sh));
+    }
+    if (u == 0) {
+      uint8_t hb[12];
+      int pos = 0;
+      hb[pos++] = 0x0a;
+      uint32_t v = l1;
+      while (v >= 0x80) { hb[pos++] = (uint8_t)(v | 0x80); v >>= 7; }
+      hb[pos++] = (uint8_t)v;
+      hb[pos++] = 0x32;
+      v = l2;
+      while (v >= 0x80) { hb[pos++] = (uint8_t)(v | 0x80); v >>= 7; }
+      hb[pos++] = (uint8_t)v;
+      const int ob = r * row_bytes;
+      for (int b = 0; b < pos; ++b) atomicOr(sm_words + ((ob + b) >> 2), (uint32_t)hb[b] << (((ob + b) & 3) * 8));
+    }
+    r += dr; u += du;
+    if (u >= q) { u -= q; ++r; }
+  }
+}
+
+template <typename TIn>
+__global__ void __launch_bounds__(256)
+pack_listvalue_ring4(const TIn* __restrict__ in, int64_t rows, int cols, int row_bytes, int hdr, uint32_t l1, uint32_t l2,
+                     int R, int slot_bytes, uint8_t* __restrict__ out) {
+  extern __shared__ __align__(128) uint8_t lv_ring[];  // [kLvPackSlots][slot_bytes]
+  const int64_t nchunks = (rows + R - 1) / R;
+  const int q = cols >> 2;
+  int64_t i = 0;
+  for (int64_t ch = blockIdx.x; ch < nchunks; ch += gridDim.x, ++i) {
+    const int64_t r0 = ch * R;
+    const int nr = (int)min((int64_t)R, rows - r0);
+    const int nbytes = nr * row_bytes;
+    uint8_t* slot = lv_ring + (size_t)(i % kLvPackSlots) * slot_bytes;
+    // the bulk store that last read this slot (kLvPackSlots chunks ago) must have finished reading it
+    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kLvPackSlots - 1) : "memory");
+    __syncthreads();
+    for (int v = threadIdx.x; v < ((nbytes + 15) >> 4) + 1; v += blockDim.x)
+      reinterpret_cast<uint4*>(slot)[v] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();
+    pack4_chunk(reinterpret_cast<uint32_t*>(slot), in, r0, nr, cols, q, row_bytes, hdr, l1, l2);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic stores -> visible to the bulk copy engine
+    __syncthreads();
+    uint8_t* dst = out + r0 * (int64_t)row_bytes;
+    const uint32_t bytes = (uint32_t)nbytes & ~15u;
+    if (threadIdx.x == 0) {
+      if (bytes)
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                     ::"l"(dst), "r"((uint32_t)__cvta_generic_to_shared(slot)), "r"(bytes) : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+    for (int b = (int)bytes + threadIdx.x; b < nbytes; b += blockDim.x) dst[b] = slot[b];  // last chunk's tail
+  }
+  if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 // rows per staged chunk: a multiple of 16 with the chunk near 32 KB; 0 = row too long for shared memory
@@ -400,6 +562,18 @@ int staged_rows(int64_t row_bytes) {
   if (m < 1) m = 1;
   return (int)(16 * m);
 }
+
+// ring kernels: rows per chunk (a multiple of 16) and bytes per ring slot; 0 rows = do not use them
+int ring_rows(int64_t row_bytes, int stages) {
+  static const int enabled = getenv("SB200_LV_RING") ? atoi(getenv("SB200_LV_RING")) : 1;
+  static const int64_t target = getenv("SB200_LV_RING_CHUNK") ? atoll(getenv("SB200_LV_RING_CHUNK")) : 12 * 1024;
+  if (!enabled) return 0;
+  int64_t m = target / (row_bytes * 16);
+  if (m < 1) m = 1;
+  if ((m * 16 * row_bytes + 192) * stages > 200 * 1024) return 0;
+  return (int)(16 * m);
+}
+int ring_slot_bytes(int64_t row_bytes, int R) { return (int)(((int64_t)R * row_bytes + 64 + 127) & ~(int64_t)127); }
 
 int grid_for(int64_t total, int per_thread) {
   int64_t want = sb::ceil_div(total, 256 * (int64_t)per_thread);
@@ -461,7 +635,18 @@ extern "C" int32_t sb_unpack_listvalue(const uint8_t* d_wire, uint64_t nbytes, i
     SB_CUDA(cudaFuncSetAttribute(unpack_listvalue_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     int64_t nch = sb::ceil_div(rows, R);
     int grid = (int)(nch < (int64_t)sb::kNumSMs * 12 ? nch : (int64_t)sb::kNumSMs * 12);
-    if (cols % 4 == 0) {
+    const int RR = cols % 4 == 0 ? ring_rows(rb, kLvStages) : 0;
+    if (RR > 0) {
+      const int sb = ring_slot_bytes(rb, RR);
+      const size_t rsm = (size_t)kLvStages * sb;
+      SB_CUDA(cudaFuncSetAttribute(unpack_listvalue_ring4, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      const int64_t nch2 = sb::ceil_div(rows, RR);
+      const int per_sm = (int)(200 * 1024 / (rsm + 1024)) < 8 ? (int)(200 * 1024 / (rsm + 1024)) : 8;
+      const int64_t gmax = (int64_t)sb::kNumSMs * (per_sm > 0 ? per_sm : 1);
+      unpack_listvalue_ring4<<<(int)(nch2 < gmax ? nch2 : gmax), 256, rsm, st>>>(d_wire, rows, (int)cols, (int)rb, hdr,
+                                                                              (uint32_t)l1, (uint32_t)l2, RR, sb, d_out,
+                                                                              ld, d_status);
+    } else if (cols % 4 == 0) {
       SB_CUDA(cudaFuncSetAttribute(unpack_listvalue_staged4, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       unpack_listvalue_staged4<<<grid, 256, smem, st>>>(d_wire, rows, (int)cols, (int)rb, hdr, (uint32_t)l1, (uint32_t)l2,
                                                        R, d_out, ld, d_status);
@@ -506,7 +691,24 @@ extern "C" int32_t sb_pack_listvalue(const void* d_in, int32_t in_dtype, int64_t
     const size_t smem = (size_t)R * rb + 64;
     int64_t nch = sb::ceil_div(rows, R);
     int g2 = (int)(nch < (int64_t)sb::kNumSMs * 12 ? nch : (int64_t)sb::kNumSMs * 12);
-    if (cols > 0 && cols % 4 == 0 && in_dtype == SB_F32) {
+    const int RR = (cols > 0 && cols % 4 == 0) ? ring_rows(rb, kLvPackSlots) : 0;
+    if (RR > 0) {
+      const int sb = ring_slot_bytes(rb, RR);
+      const size_t rsm = (size_t)kLvPackSlots * sb;
+      const int64_t nch2 = sb::ceil_div(rows, RR);
+      const int per_sm = (int)(200 * 1024 / (rsm + 1024)) < 8 ? (int)(200 * 1024 / (rsm + 1024)) : 8;
+      const int64_t gmax = (int64_t)sb::kNumSMs * (per_sm > 0 ? per_sm : 1);
+      const int g3 = (int)(nch2 < gmax ? nch2 : gmax);
+      if (in_dtype == SB_F32) {
+        SB_CUDA(cudaFuncSetAttribute(pack_listvalue_ring4<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        pack_listvalue_ring4<float><<<g3, 256, rsm, st>>>((const float*)d_in, rows, (int)cols, (int)rb, hdr, (uint32_t)l1,
+                                                         (uint32_t)l2, RR, sb, d_wire);
+      } else {
+        SB_CUDA(cudaFuncSetAttribute(pack_listvalue_ring4<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        pack_listvalue_ring4<int32_t><<<g3, 256, rsm, st>>>((const int32_t*)d_in, rows, (int)cols, (int)rb, hdr,
+                                                           (uint32_t)l1, (uint32_t)l2, RR, sb, d_wire);
+      }
+    } else if (cols > 0 && cols % 4 == 0 && in_dtype == SB_F32) {
       SB_CUDA(cudaFuncSetAttribute(pack_listvalue_staged4<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       pack_listvalue_staged4<float><<<g2, 256, smem, st>>>((const float*)d_in, rows, (int)cols, (int)rb, hdr, (uint32_t)l1,
                                                           (uint32_t)l2, R, d_wire);
