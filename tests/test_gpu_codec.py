@@ -75,3 +75,27 @@ def test_round_trip_property_large():
     assert torch.equal(codec.decode_tensor(codec.encode_tensor(t)), t)
     t2 = t[:20000]
     assert torch.equal(codec.decode_ndarray(codec.encode_ndarray(t2), 64), t2)
+
+
+@pytest.mark.parametrize("shape", [(16, 8), (17, 8), (4097, 8), (33, 128), (100, 1024)])
+def test_ndarray_ring_kernels_round_trip_and_bytes(shape):
+    """cols % 4 == 0 takes the bulk-copy ring kernels: chunk boundaries, the < 16-byte tail of the last chunk."""
+    import torch
+
+    a = np.random.RandomState(5).randn(*shape).astype(np.float32)
+    wire = ocodec.encode_listvalue(a.astype(np.float64))
+    assert np.array_equal(codec.decode_ndarray(wire, shape[1]).cpu().numpy(), a)
+    assert codec.encode_ndarray(torch.from_numpy(a).cuda()) == wire
+
+
+def test_ndarray_ring_kernel_rejects_bad_tag_in_a_late_chunk():
+    a = np.random.RandomState(6).randn(1000, 8)
+    wire = bytearray(ocodec.encode_listvalue(a))
+    row_bytes, hdr = ocodec.listvalue_row_layout(8)
+    wire[937 * row_bytes + hdr + 11 * 5 + 2] = 0x19  # fixed64 tag of row 937, column 5 -> another field number
+    with pytest.raises(SeldonB200Error):
+        codec.decode_ndarray(bytes(wire), 8)
+    wire = bytearray(ocodec.encode_listvalue(a))
+    wire[500 * row_bytes] = 0x12  # row header tag
+    with pytest.raises(SeldonB200Error):
+        codec.decode_ndarray(bytes(wire), 8)
