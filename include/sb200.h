@@ -72,6 +72,19 @@ int32_t sb_combiner_mean(const float* const* h_inputs, int32_t n_children, int64
 int32_t sb_standardise(const float* d_in, int64_t rows, int64_t cols, int64_t ld_in, const float* d_mu,
                        const float* d_inv_sigma, float* d_out, int64_t ld_out, uintptr_t stream);
 
+/* ------------------------------------------------------------------------------------- feedback metrics
+ * replaces components/outlier-detection/mahalanobis/utils.py:106-142 (performance, outlier_stats: confusion matrix,
+ * accuracy / precision / recall / F1 / F2 over all feedback and over the last roll_window observations, outlier
+ * counts) as called by OutlierMahalanobis.send_feedback (OutlierMahalanobis.py:34-66, roll_window = 100 at L30).
+ * The history is a caller-owned device buffer of sb_feedback_state_bytes(roll_window) bytes (four counters, two
+ * sums, a ring of the last roll_window pairs); reset once, then one update per feedback batch.
+ * d_metrics18 receives, in the reference's order: tn fp fn tp | acc prec rec f1 f2 (total) | acc prec rec f1 f2
+ * (rolling) | predicted outliers (rolling), labelled outliers (rolling), predicted (total), labelled (total). */
+uint64_t sb_feedback_state_bytes(int32_t roll_window);
+int32_t sb_feedback_reset(void* d_state, int32_t roll_window, uintptr_t stream);
+int32_t sb_feedback_update(const int32_t* d_pred, const int32_t* d_truth, int64_t n, void* d_state,
+                           double* d_metrics18, uintptr_t stream);
+
 /* ------------------------------------------------------------------------------------------ mahalanobis
  * replaces components/outlier-detection/mahalanobis/CoreMahalanobis.py.
  * create: the constructor L26-40 (same parameters; d = number of features, fixed per handle).

@@ -106,6 +106,34 @@ def combiner_case():
     print("combiner_mnist: ok")
 
 
+def feedback_case():
+    """Feedback metrics: the reference's own performance / outlier_stats (utils.py:106-142, imported unmodified) on a
+    stream of feedback batches; one row of 18 numbers per batch."""
+    import importlib.util
+    import warnings
+
+    spec = importlib.util.spec_from_file_location(
+        "ref_maha_utils", "/root/reference/components/outlier-detection/mahalanobis/utils.py")
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    rs = np.random.RandomState(11)
+    sizes = [1, 1, 1, 3, 7, 50, 120, 1, 260, 5]
+    preds, labels, rows = [], [], []
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")  # undefined precision / recall on the first all-negative batches
+        for i, nb in enumerate(sizes):
+            y = (rs.rand(nb) < (0.0 if i < 2 else 0.2)).astype(np.int64)
+            p = np.where(rs.rand(nb) < 0.8, y, 1 - y)
+            labels.append(y)
+            preds.append(p)
+            yy, pp = np.concatenate(labels), np.concatenate(preds)
+            rows.append([float(v) for v in ref.performance(yy, pp, roll_window=100)] +
+                        [float(v) for v in ref.outlier_stats(yy, pp, roll_window=100)])
+    np.savez_compressed(os.path.join(OUT, "feedback_stream.npz"), sizes=np.array(sizes), pred=np.concatenate(preds),
+                        truth=np.concatenate(labels), metrics=np.array(rows))
+    print("feedback_stream", len(sizes), "batches")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     if not ref_shim.available():
@@ -130,6 +158,7 @@ def main():
     router_case("thompson_32", 1, 32, 1, 3000)
     router_case("thompson_2_rows", 1, 2, 3, 3000, rows_mod=7)
     combiner_case()
+    feedback_case()
 
 
 if __name__ == "__main__":

@@ -10,6 +10,7 @@ plus `codec` (SeldonMessage tensor / ndarray payloads) and `dist` (row-sharded b
 """
 from .errors import SeldonB200Error  # noqa: F401
 from .outlier import OutlierMahalanobisB200  # noqa: F401
+from .feedback import OutlierMahalanobisFeedbackB200  # noqa: F401
 from .routers import EpsilonGreedyB200, ThompsonSamplingB200  # noqa: F401
 from .combiner import MeanCombinerB200  # noqa: F401
 from .transformer import StandardiseB200  # noqa: F401

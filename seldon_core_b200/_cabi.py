@@ -30,6 +30,9 @@ SIGNATURES = {
     "sb_tensor_values_offset": (c_uint64, [c_int64, c_int64]),
     "sb_combiner_mean": (c_int32, [POINTER(c_void_p), c_int32, c_int64, c_void_p, _uintptr]),
     "sb_standardise": (c_int32, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64, _uintptr]),
+    "sb_feedback_state_bytes": (c_uint64, [c_int32]),
+    "sb_feedback_reset": (c_int32, [c_void_p, c_int32, _uintptr]),
+    "sb_feedback_update": (c_int32, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, _uintptr]),
     "sb_maha_create": (c_int32, [_pp, c_int32, c_int32, c_double, c_double, c_int64, c_int64]),
     "sb_maha_destroy": (c_int32, [c_void_p]),
     "sb_maha_workspace_bytes": (c_int32, [c_void_p, c_int64, POINTER(c_uint64)]),
