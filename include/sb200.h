@@ -61,6 +61,22 @@ int32_t sb_pack_listvalue(const void* d_in, int32_t in_dtype, int64_t rows, int6
 uint64_t sb_listvalue_nbytes(int64_t rows, int64_t cols);
 uint64_t sb_tensor_values_offset(int64_t rows, int64_t cols);
 
+/* REST JSON: the text of a numeric "ndarray" value ([[..],[..]] or [..], whitespace allowed, NaN / Infinity /
+ * -Infinity as CPython's json module writes them) -> fp32 matrix.  Replaces json.loads + np.array(datadef["ndarray"])
+ * of python/seldon_core/utils.py:499-505 (extract_request_parts_json); numbers are converted with correct rounding to
+ * binary64 (what float() does inside json.loads) and then narrowed to fp32 like the Tensor path.
+ * Step 1: sb_json_ndarray_count fills d_counts4 = {numbers, '[' count, ']' count, characters that cannot occur in a
+ * numeric array} and leaves per-chunk prefixes in the workspace (sb_json_workspace_bytes(nbytes) bytes, 8-byte
+ * aligned).  The caller derives rows = '[' count - 1 (or 1 for a flat list) and cols = numbers / rows.
+ * Step 2: sb_unpack_json_ndarray with the same text and workspace stores the values; *d_status is 0 when every token
+ * was a number and every row has cols entries, 1 for malformed text, 2 for a number with more than 19 significant
+ * digits whose rounding cannot be decided in 128-bit arithmetic. */
+uint64_t sb_json_workspace_bytes(uint64_t nbytes);
+int32_t sb_json_ndarray_count(const uint8_t* d_text, uint64_t nbytes, void* d_ws, uint64_t ws_bytes, int64_t* d_counts4,
+                              uintptr_t stream);
+int32_t sb_unpack_json_ndarray(const uint8_t* d_text, uint64_t nbytes, int64_t rows, int64_t cols, const void* d_ws,
+                               float* d_out, int64_t ld, int32_t* d_status, uintptr_t stream);
+
 /* --------------------------------------------------------------------------------------------- combiner
  * replaces examples/combiners/mnist_combiner/MnistCombiner.py:8-11 and the N-child rule of
  * engine/src/main/java/io/seldon/engine/predictors/AverageCombinerUnit.java:35-79: out = (sum_j in_j) / N,

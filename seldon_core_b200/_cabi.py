@@ -30,6 +30,10 @@ SIGNATURES = {
     "sb_tensor_values_offset": (c_uint64, [c_int64, c_int64]),
     "sb_combiner_mean": (c_int32, [POINTER(c_void_p), c_int32, c_int64, c_void_p, _uintptr]),
     "sb_standardise": (c_int32, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64, _uintptr]),
+    "sb_json_workspace_bytes": (c_uint64, [c_uint64]),
+    "sb_json_ndarray_count": (c_int32, [c_void_p, c_uint64, c_void_p, c_uint64, c_void_p, _uintptr]),
+    "sb_unpack_json_ndarray": (c_int32, [c_void_p, c_uint64, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p,
+                                         _uintptr]),
     "sb_feedback_state_bytes": (c_uint64, [c_int32]),
     "sb_feedback_reset": (c_int32, [c_void_p, c_int32, _uintptr]),
     "sb_feedback_update": (c_int32, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, _uintptr]),

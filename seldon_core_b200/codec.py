@@ -5,6 +5,8 @@ Host-side mirror of the numeric branches of ``python/seldon_core/utils.py``: ``g
 (``python/seldon_core/user_model.py:103-131``).  Only the small varint headers are handled on the host; the bulk
 (the packed doubles / the 11-byte ListValue records) is converted by libsb200.so on the GPU.
 """
+import re
+
 import numpy as np
 
 from . import _cabi
@@ -168,3 +170,71 @@ def class_names(result_ndim, n_targets, user_names=None):
     if result_ndim > 1:
         return list(user_names) if user_names is not None else ["t:{}".format(i) for i in range(n_targets)]
     return []
+
+
+# ---------------------------------------------------------------------------------------------- REST JSON
+_NDARRAY_KEY = re.compile(rb'"ndarray"\s*:\s*\[')
+_END_2D = re.compile(rb'\]\s*\]')
+
+
+def json_ndarray_span(payload):
+    """(start, end, ndim) of the value of "ndarray" in a REST request body (`{"data": {"ndarray": [[..], ..]}}`,
+    utils.py:499-505), found without parsing the numbers: start at its opening bracket, end one past its closing one."""
+    m = _NDARRAY_KEY.search(payload)
+    if m is None:
+        raise SeldonB200Error('no "ndarray" member in the payload')
+    start = m.end() - 1
+    i = start + 1
+    while i < len(payload) and payload[i:i + 1] in (b" ", b"\n", b"\r", b"\t"):
+        i += 1
+    if payload[i:i + 1] == b"[":
+        e = _END_2D.search(payload, i)
+        if e is None:
+            raise SeldonB200Error('unterminated "ndarray" value')
+        return start, e.end(), 2
+    e = payload.find(b"]", start)
+    if e < 0:
+        raise SeldonB200Error('unterminated "ndarray" value')
+    return start, e + 1, 1
+
+
+def decode_json_ndarray(payload, device=None):
+    """REST JSON body (bytes) -> CUDA float32 array holding data.ndarray, shape (rows, cols) or (n,) for a flat list.
+
+    Replaces `json.loads` + `np.array(datadef["ndarray"])` (utils.py:499-505): every number gets the correctly rounded
+    binary64 value CPython's float() gives it, narrowed to fp32.  Non-numeric or ragged arrays raise."""
+    import torch
+
+    if isinstance(payload, str):
+        payload = payload.encode("utf-8")
+    start, end, ndim = json_ndarray_span(payload)
+    text = payload[start:end]
+    dev = _device(device)
+    L = _cabi.lib()
+    buf = torch.frombuffer(bytearray(text), dtype=torch.uint8).to(dev)
+    ws = torch.empty((int(L.sb_json_workspace_bytes(len(text))) + 7) // 8, dtype=torch.int64, device=dev)
+    counts = torch.zeros(4, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream().cuda_stream
+        _cabi.check(L.sb_json_ndarray_count(buf.data_ptr(), len(text), ws.data_ptr(), ws.numel() * 8, counts.data_ptr(),
+                                            stream))
+        numbers, nopen, nclose, nbad = (int(v) for v in counts.cpu())
+        if nbad or nopen != nclose or nopen != (1 if ndim == 1 else nopen) or nopen < ndim:
+            raise SeldonB200Error('"ndarray" is not an array of numbers')
+        rows = 1 if ndim == 1 else nopen - 1
+        if rows == 0 or numbers % max(rows, 1):
+            if numbers == 0:
+                return torch.empty((0,) if ndim == 1 or rows == 0 else (rows, 0), dtype=torch.float32, device=dev)
+            raise SeldonB200Error('"ndarray" rows have different lengths')
+        cols = numbers // rows
+        out = torch.empty((rows, cols), dtype=torch.float32, device=dev)
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+        _cabi.check(L.sb_unpack_json_ndarray(buf.data_ptr(), len(text), rows, cols, ws.data_ptr(), out.data_ptr(), cols,
+                                             status.data_ptr(), stream))
+        st = int(status.item())
+    if st == 2:
+        raise SeldonB200Error('"ndarray" holds a number with more than 19 significant digits that needs arbitrary '
+                              'precision to round; not supported')
+    if st != 0:
+        raise SeldonB200Error('"ndarray" is not a rectangular array of JSON numbers')
+    return out.view(-1) if ndim == 1 else out

@@ -84,6 +84,45 @@ def codec_bench():
     emit("unpack ndarray ListValue (2Mi x 64)", "values/s", rows * cols, nb + 4 * rows * cols, best, med)
 
 
+def json_bench():
+    """REST JSON ndarray text -> fp32: 4096 rows of json.dumps output tiled to 1 Mi rows x 64 (about 1.3 GB of text)."""
+    import time
+
+    import numpy as np
+
+    L = _cabi.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    block_rows, cols, tiles = 4096, 64, 256
+    a = np.random.RandomState(0).randn(block_rows, cols).astype(np.float32).astype(np.float64)
+    inner = json.dumps(a.tolist())[1:-1]                       # "[..], [..], ..." without the outer brackets
+    text = ("[" + ", ".join([inner] * tiles) + "]").encode()
+    rows = block_rows * tiles
+    t0 = time.perf_counter()
+    ref = np.array(json.loads(b'{"data":{"ndarray":[' + inner.encode() + b']}}')["data"]["ndarray"])
+    cpu_s = time.perf_counter() - t0
+    buf = torch.frombuffer(bytearray(text), dtype=torch.uint8).cuda()
+    nbytes = len(text)
+    ws = torch.empty((int(L.sb_json_workspace_bytes(nbytes)) + 7) // 8, dtype=torch.int64, device="cuda")
+    counts = torch.zeros(4, dtype=torch.int64, device="cuda")
+    out = torch.empty((rows, cols), dtype=torch.float32, device="cuda")
+    status = torch.zeros(1, dtype=torch.int32, device="cuda")
+
+    def run():
+        _cabi.check(L.sb_json_ndarray_count(buf.data_ptr(), nbytes, ws.data_ptr(), ws.numel() * 8, counts.data_ptr(), st))
+        _cabi.check(L.sb_unpack_json_ndarray(buf.data_ptr(), nbytes, rows, cols, ws.data_ptr(), out.data_ptr(), cols,
+                                             status.data_ptr(), st))
+
+    best, med = timed(run)
+    assert int(status.item()) == 0 and [int(v) for v in counts.cpu()] == [rows * cols, rows + 1, rows + 1, 0]
+    assert np.array_equal(out[:block_rows].cpu().numpy(), ref.astype(np.float32))
+    assert torch.equal(out[-block_rows:], out[:block_rows])
+    emit("unpack REST JSON ndarray text (1Mi x 64, %.2f GB, %.1f B/value)" % (nbytes / 1e9, nbytes / (rows * cols)),
+         "values/s", rows * cols, nbytes + 4 * rows * cols, best, med,
+         {"cpu_reference_values_per_s": block_rows * cols / cpu_s,
+          "cpu_reference": "json.loads + np.array on one 4096-row block (utils.py:499-505), one host thread",
+          "note": "two passes over the text (count, parse): DRAM traffic is about 2x the algorithmic bytes"})
+
+
 def routers():
     for kind, T in (("eps", 10_000_000), ("thompson", 1_000_000)):
         p, u = synth.router_rewards(T, 32)
@@ -106,10 +145,12 @@ def routers():
 
 if __name__ == "__main__":
     print(json.dumps({"gpu": torch.cuda.get_device_name(0), "hbm_peak_gbs": HBM}))
-    which = sys.argv[1:] or ["combiner", "codec", "routers"]
+    which = sys.argv[1:] or ["combiner", "codec", "json", "routers"]
     if "combiner" in which:
         combiner()
     if "codec" in which:
         codec_bench()
+    if "json" in which:
+        json_bench()
     if "routers" in which:
         routers()
