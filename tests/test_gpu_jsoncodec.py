@@ -10,7 +10,7 @@ from seldon_core_b200.errors import SeldonB200Error
 pytestmark = pytest.mark.gpu
 
 
-def ref_decode(payload):
+def ref_decode(payload):  # = oracle.jsoncodec.decode
     """extract_request_parts_json, ndarray branch: utils.py:499-505, narrowed like every other decode path."""
     with np.errstate(over="ignore"):  # doubles beyond the fp32 range narrow to inf, as on the device
         return np.array(json.loads(payload)["data"]["ndarray"]).astype(np.float32)
