@@ -212,13 +212,173 @@ __device__ double np_beta(DevMt& g, double a, double b) {
   return ga / __dadd_rn(ga, gb);
 }
 
+// ---- Thompson sampling: the NumPy stream through a look-ahead window ------------------------------------------
+// A route draws n beta variates = 2n gamma variates one after the other from one MT19937 stream; evaluated draw by
+// draw (np_beta above) that is ~600 dependent fp64 instructions per gamma, 50 us per route at 32 arms - the speed of the
+// CPU reference.  The stream positions a draw will read are not known in advance (rejection sampling), but everything
+// expensive depends only on the POSITION: the uniform at double-index i, and the polar Gaussian attempt that starts at
+// i (two uniforms, a log, a square root, a division).  So the 32 lanes fill tables for the next kWinD positions in
+// parallel, and the sequential walk over the arms (same branches, same arithmetic, same order of consumption as
+// rk_beta / rk_standard_gamma / rk_gauss of NumPy's legacy generator) only looks values up.
+constexpr int kWinD = 304;  // doubles per window: 2 * (kWinD + 2) words span at most two 624-word blocks
+
+struct NpWindow {
+  uint32_t* blk[2];  // shared: the committed block and the block after it
+  int cur, next_valid;
+  int pos;           // word position in blk[cur] where the window starts (0 .. 624)
+  int head;          // doubles consumed from the window
+  int has_gauss;
+  double gauss;
+  int fail;          // a single beta draw ran past the window (probability ~1e-20): reported to the host
+  double *U, *gret, *gcache, *E;
+  uint8_t* ok;
+  int have_E;
+};
+
+__device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
+  y ^= y >> 11;
+  y ^= (y << 7) & 0x9d2c5680u;
+  y ^= (y << 15) & 0xefc60000u;
+  y ^= y >> 18;
+  return y;
+}
+
+// move the committed position to the first unconsumed word and fill the tables from there
+__device__ void np_window_build(NpWindow& w, bool want_E) {
+  const int lane = threadIdx.x & 31;
+  int p = w.pos + 2 * w.head;
+  if (p > MT_N) {  // past the end of the committed block: the next block becomes the committed one
+    if (!w.next_valid) {
+      for (int i = lane; i < MT_N; i += 32) w.blk[w.cur ^ 1][i] = w.blk[w.cur][i];
+      mt_regenerate(w.blk[w.cur ^ 1]);
+    }
+    w.cur ^= 1;
+    w.next_valid = 0;
+    p -= MT_N;
+  }
+  w.pos = p;
+  w.head = 0;
+  if (p + 2 * (kWinD + 2) > MT_N && !w.next_valid) {
+    __syncwarp();
+    for (int i = lane; i < MT_N; i += 32) w.blk[w.cur ^ 1][i] = w.blk[w.cur][i];
+    mt_regenerate(w.blk[w.cur ^ 1]);
+    w.next_valid = 1;
+  }
+  __syncwarp();
+  const uint32_t* b0 = w.blk[w.cur];
+  const uint32_t* b1 = w.blk[w.cur ^ 1];
+  for (int i = lane; i < kWinD + 2; i += 32) {
+    const int k = p + 2 * i;
+    const uint32_t wa = mt_temper(k < MT_N ? b0[k] : b1[k - MT_N]);
+    const uint32_t wb = mt_temper(k + 1 < MT_N ? b0[k + 1] : b1[k + 1 - MT_N]);
+    w.U[i] = ((double)(wa >> 5) * 67108864.0 + (double)(wb >> 6)) / 9007199254740992.0;
+  }
+  __syncwarp();
+  for (int i = lane; i < kWinD; i += 32) {
+    const double x1 = 2.0 * w.U[i] - 1.0, x2 = 2.0 * w.U[i + 1] - 1.0;
+    const double r2 = __dadd_rn(__dmul_rn(x1, x1), __dmul_rn(x2, x2));
+    const bool good = !(r2 >= 1.0 || r2 == 0.0);
+    w.ok[i] = good;
+    if (good) {
+      const double f = sqrt(__dmul_rn(-2.0, log(r2)) / r2);
+      w.gcache[i] = __dmul_rn(f, x1);
+      w.gret[i] = __dmul_rn(f, x2);
+    }
+    if (want_E) w.E[i] = -log(1.0 - w.U[i]);
+  }
+  w.have_E = want_E;
+  __syncwarp();
+}
+
+__device__ __forceinline__ double win_double(NpWindow& w) {
+  if (w.head >= kWinD) { w.fail = 1; w.head = kWinD - 1; }
+  return w.U[w.head++];
+}
+__device__ __forceinline__ double win_exponential(NpWindow& w) {
+  if (w.head >= kWinD) { w.fail = 1; w.head = kWinD - 1; }
+  const int i = w.head++;
+  return w.have_E ? w.E[i] : -log(1.0 - w.U[i]);
+}
+__device__ __forceinline__ double win_gauss(NpWindow& w) {
+  if (w.has_gauss) {
+    const double t = w.gauss;
+    w.has_gauss = 0;
+    w.gauss = 0.0;
+    return t;
+  }
+  while (w.head < kWinD - 1 && !w.ok[w.head]) w.head += 2;
+  if (w.head >= kWinD - 1) { w.fail = 1; w.head = kWinD - 2; return 0.0; }
+  const int i = w.head;
+  w.head += 2;
+  w.gauss = w.gcache[i];
+  w.has_gauss = 1;
+  return w.gret[i];
+}
+
+// rk_standard_gamma of the legacy generator, reading the stream through the window (same arithmetic as np_std_gamma)
+__device__ double win_std_gamma(NpWindow& w, double shape) {
+  if (shape == 1.0) return win_exponential(w);
+  if (shape == 0.0) return 0.0;
+  if (shape < 1.0) {
+    for (;;) {
+      const double u = win_double(w), v = win_exponential(w);
+      if (w.fail) return 0.0;
+      if (u <= 1.0 - shape) {
+        const double x = pow(u, 1.0 / shape);
+        if (x <= v) return x;
+      } else {
+        const double y = -log((1 - u) / shape);
+        const double x = pow(__dadd_rn(1.0 - shape, __dmul_rn(shape, y)), 1.0 / shape);
+        if (x <= __dadd_rn(v, y)) return x;
+      }
+    }
+  }
+  const double b = shape - 1.0 / 3.0, c = 1.0 / sqrt(9 * b);
+  for (;;) {
+    double x, v;
+    do {
+      x = win_gauss(w);
+      v = __dadd_rn(1.0, __dmul_rn(c, x));
+    } while (v <= 0.0 && !w.fail);
+    v = __dmul_rn(__dmul_rn(v, v), v);
+    const double u = win_double(w);
+    if (w.fail) return 0.0;
+    const double x2 = __dmul_rn(x, x);
+    if (u < __dadd_rn(1.0, -__dmul_rn(__dmul_rn(0.0331, x2), x2))) return __dmul_rn(b, v);
+    const double rhs = __dadd_rn(__dmul_rn(__dmul_rn(0.5, x), x), __dmul_rn(b, __dadd_rn(__dadd_rn(1.0, -v), log(v))));
+    if (log(u) < rhs) return __dmul_rn(b, v);
+  }
+}
+
+__device__ double win_beta(NpWindow& w, double a, double b) {
+  if (a <= 1.0 && b <= 1.0) {
+    for (;;) {
+      const double u = win_double(w), v = win_double(w);
+      if (w.fail) return 0.0;
+      const double x = pow(u, 1.0 / a), y = pow(v, 1.0 / b);
+      const double xpy = __dadd_rn(x, y);
+      if (xpy <= 1.0 && __dadd_rn(u, v) > 0.0) {
+        if (xpy > 0) return x / xpy;
+        double lx = log(u) / a, ly = log(v) / b;
+        const double lm = lx > ly ? lx : ly;
+        lx -= lm; ly -= lm;
+        return exp(lx - log(__dadd_rn(exp(lx), exp(ly))));
+      }
+    }
+  }
+  const double ga = win_std_gamma(w, a), gb = win_std_gamma(w, b);
+  return ga / __dadd_rn(ga, gb);
+}
+
 // T calls.  kind 0 = epsilon-greedy, 1 = Thompson.  reward_mode -1: route only.
 __global__ void __launch_bounds__(32)
 router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon, long long T,
                   const long long* __restrict__ rows, const float* __restrict__ reward,
                   const float* __restrict__ arm_p, int reward_mode, int* __restrict__ decisions, int forced_arm,
                   double forced_reward, long long forced_rows) {
-  __shared__ uint32_t s_py[MT_N], s_np[MT_N];
+  __shared__ uint32_t s_py[MT_N], s_np[MT_N], s_np2[MT_N];
+  __shared__ double s_U[kWinD + 2], s_gret[kWinD], s_gcache[kWinD], s_E[kWinD];
+  __shared__ uint8_t s_ok[kWinD];
   __shared__ long long s_succ[kMaxArms], s_tries[kMaxArms];
   __shared__ double s_val[kMaxArms];
   const int lane = threadIdx.x;
@@ -232,6 +392,12 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
   DevMt np{s_np, st->np.pos, st->np.has_gauss, st->np.gauss};
   int best = st->best;
   __syncwarp();
+  // Thompson: the NumPy stream is read through a window (committed position = np.pos at entry)
+  NpWindow win{{s_np, s_np2}, 0, 0, np.pos, 0, np.has_gauss, np.gauss, 0, s_U, s_gret, s_gcache, s_E, s_ok, 0};
+  const bool windowed = kind == 1 && forced_arm < 0;
+  // room one beta draw may need: two gammas, each a few doubles per trial; a refill is forced below this margin
+  constexpr int kArmMargin = 48;
+  int win_built = 0;
   for (long long t = 0; t < T; ++t) {
     int arm;
     if (forced_arm >= 0) {
@@ -246,10 +412,24 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
     } else {
       double top = 0.0;
       arm = 0;
+      // unit shapes draw an exponential: tabulate -log(1 - U) with the window when some arm still has one
+      bool unit = false;
+      for (int j = lane; j < n; j += 32) unit |= s_succ[j] == 0 || s_tries[j] == s_succ[j];
+      unit = __any_sync(0xffffffffu, unit);
       for (int j = 0; j < n; ++j) {  // ThompsonSampling.py:81-82, arm order; np.argmax = first maximum
+        if (!win_built || kWinD - win.head < kArmMargin) {
+          np_window_build(win, unit);
+          win_built = 1;
+        }
         const double a = (double)(1 + s_succ[j]), b = (double)(1 + s_tries[j] - s_succ[j]);
-        const double v = np_beta(np, a, b);
+        const double v = win_beta(win, a, b);
         if (j == 0 || v > top) { top = v; arm = j; }
+      }
+      if (win.fail) {
+        // one beta draw needed more than kArmMargin doubles (probability ~1e-20): this and the remaining calls are
+        // reported as -1 and the state is left at the last completed call's feedback
+        for (long long u = t + lane; u < T; u += 32) decisions[u] = -1;
+        break;
       }
     }
     if (lane == 0 && forced_arm < 0) decisions[t] = arm;
@@ -295,7 +475,25 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
     }
   }
   __syncwarp();
-  for (int i = lane; i < MT_N; i += 32) { st->py.mt[i] = s_py[i]; st->np.mt[i] = s_np[i]; }
+  const uint32_t* np_blk = s_np;
+  if (windowed && win_built) {
+    // commit the consumed part of the window: the state a draw-by-draw generator would be in
+    int p = win.pos + 2 * win.head;
+    if (p > MT_N) {
+      if (!win.next_valid) {
+        for (int i = lane; i < MT_N; i += 32) win.blk[win.cur ^ 1][i] = win.blk[win.cur][i];
+        mt_regenerate(win.blk[win.cur ^ 1]);
+      }
+      win.cur ^= 1;
+      p -= MT_N;
+    }
+    np.pos = p;
+    np.has_gauss = win.has_gauss;
+    np.gauss = win.gauss;
+    np_blk = win.blk[win.cur];
+    __syncwarp();
+  }
+  for (int i = lane; i < MT_N; i += 32) { st->py.mt[i] = s_py[i]; st->np.mt[i] = np_blk[i]; }
   for (int j = lane; j < n; j += 32) { st->succ[j] = s_succ[j]; st->tries[j] = s_tries[j]; }
   if (lane == 0) {
     st->py.pos = py.pos;

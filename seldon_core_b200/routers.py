@@ -107,6 +107,9 @@ class _RouterBase(object):
             with torch.cuda.device(self._device):
                 _cabi.check(_cabi.lib().sb_router_run(h, 1, None, None, None, -1, out.data_ptr(), self._stream()))
             branch = int(out.item())
+            if branch < 0:
+                raise SeldonB200Error("router: a sampling draw overran its look-ahead window; router state is invalid",
+                                      status_code=500)
             if self.history:
                 self.branch_history.append(branch)
             return branch
