@@ -223,7 +223,7 @@ __device__ double np_beta(DevMt& g, double a, double b) {
 constexpr int kWinD = 304;  // doubles per window: 2 * (kWinD + 2) words span at most two 624-word blocks
 
 struct NpWindow {
-  uint32_t* blk[2];  // shared: the committed block and the block after it
+  uint32_t *blk0, *blk1;  // shared: two 624-word blocks; `cur` says which one is the committed block
   int cur, next_valid;
   int pos;           // word position in blk[cur] where the window starts (0 .. 624)
   int head;          // doubles consumed from the window
@@ -235,6 +235,8 @@ struct NpWindow {
   int have_E;
 };
 
+__device__ __forceinline__ uint32_t* win_blk(const NpWindow& w, int which) { return which ? w.blk1 : w.blk0; }
+
 __device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
   y ^= y >> 11;
   y ^= (y << 7) & 0x9d2c5680u;
@@ -243,14 +245,45 @@ __device__ __forceinline__ uint32_t mt_temper(uint32_t y) {
   return y;
 }
 
-// move the committed position to the first unconsumed word and fill the tables from there
-__device__ void np_window_build(NpWindow& w, bool want_E) {
+// The tables are filled by the whole CTA (kRouterThreads threads): warp 0 runs the bandit and posts a command, the
+// other warps wait on a named barrier, fill their share and go back to waiting.
+constexpr int kRouterThreads = 256;
+struct WinCmd { int p, cur, want_E, exit; };
+
+__device__ __forceinline__ void router_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kRouterThreads) : "memory"); }
+
+__device__ __forceinline__ void win_fill_uniforms(int tid, int p, const uint32_t* b0, const uint32_t* b1, double* U) {
+  for (int i = tid; i < kWinD + 2; i += kRouterThreads) {
+    const int k = p + 2 * i;
+    const uint32_t wa = mt_temper(k < MT_N ? b0[k] : b1[k - MT_N]);
+    const uint32_t wb = mt_temper(k + 1 < MT_N ? b0[k + 1] : b1[k + 1 - MT_N]);
+    U[i] = ((double)(wa >> 5) * 67108864.0 + (double)(wb >> 6)) / 9007199254740992.0;
+  }
+}
+__device__ __forceinline__ void win_fill_gauss(int tid, bool want_E, const double* U, double* gret, double* gcache,
+                                               double* E, uint8_t* ok) {
+  for (int i = tid; i < kWinD; i += kRouterThreads) {
+    const double x1 = 2.0 * U[i] - 1.0, x2 = 2.0 * U[i + 1] - 1.0;
+    const double r2 = __dadd_rn(__dmul_rn(x1, x1), __dmul_rn(x2, x2));
+    const bool good = !(r2 >= 1.0 || r2 == 0.0);
+    ok[i] = good;
+    if (good) {
+      const double f = sqrt(__dmul_rn(-2.0, log(r2)) / r2);
+      gcache[i] = __dmul_rn(f, x1);
+      gret[i] = __dmul_rn(f, x2);
+    }
+    if (want_E) E[i] = -log(1.0 - U[i]);
+  }
+}
+
+// move the committed position to the first unconsumed word and fill the tables from there (called by warp 0)
+__device__ __forceinline__ void np_window_build(NpWindow& w, bool want_E, WinCmd* cmd) {
   const int lane = threadIdx.x & 31;
   int p = w.pos + 2 * w.head;
   if (p > MT_N) {  // past the end of the committed block: the next block becomes the committed one
     if (!w.next_valid) {
-      for (int i = lane; i < MT_N; i += 32) w.blk[w.cur ^ 1][i] = w.blk[w.cur][i];
-      mt_regenerate(w.blk[w.cur ^ 1]);
+      for (int i = lane; i < MT_N; i += 32) win_blk(w, w.cur ^ 1)[i] = win_blk(w, w.cur)[i];
+      mt_regenerate(win_blk(w, w.cur ^ 1));
     }
     w.cur ^= 1;
     w.next_valid = 0;
@@ -260,34 +293,19 @@ __device__ void np_window_build(NpWindow& w, bool want_E) {
   w.head = 0;
   if (p + 2 * (kWinD + 2) > MT_N && !w.next_valid) {
     __syncwarp();
-    for (int i = lane; i < MT_N; i += 32) w.blk[w.cur ^ 1][i] = w.blk[w.cur][i];
-    mt_regenerate(w.blk[w.cur ^ 1]);
+    for (int i = lane; i < MT_N; i += 32) win_blk(w, w.cur ^ 1)[i] = win_blk(w, w.cur)[i];
+    mt_regenerate(win_blk(w, w.cur ^ 1));
     w.next_valid = 1;
   }
   __syncwarp();
-  const uint32_t* b0 = w.blk[w.cur];
-  const uint32_t* b1 = w.blk[w.cur ^ 1];
-  for (int i = lane; i < kWinD + 2; i += 32) {
-    const int k = p + 2 * i;
-    const uint32_t wa = mt_temper(k < MT_N ? b0[k] : b1[k - MT_N]);
-    const uint32_t wb = mt_temper(k + 1 < MT_N ? b0[k + 1] : b1[k + 1 - MT_N]);
-    w.U[i] = ((double)(wa >> 5) * 67108864.0 + (double)(wb >> 6)) / 9007199254740992.0;
-  }
+  if (lane == 0) *cmd = WinCmd{p, w.cur, want_E ? 1 : 0, 0};
   __syncwarp();
-  for (int i = lane; i < kWinD; i += 32) {
-    const double x1 = 2.0 * w.U[i] - 1.0, x2 = 2.0 * w.U[i + 1] - 1.0;
-    const double r2 = __dadd_rn(__dmul_rn(x1, x1), __dmul_rn(x2, x2));
-    const bool good = !(r2 >= 1.0 || r2 == 0.0);
-    w.ok[i] = good;
-    if (good) {
-      const double f = sqrt(__dmul_rn(-2.0, log(r2)) / r2);
-      w.gcache[i] = __dmul_rn(f, x1);
-      w.gret[i] = __dmul_rn(f, x2);
-    }
-    if (want_E) w.E[i] = -log(1.0 - w.U[i]);
-  }
+  router_bar();  // releases the helper warps with the command
+  win_fill_uniforms(lane, p, win_blk(w, w.cur), win_blk(w, w.cur ^ 1), w.U);
+  router_bar();
+  win_fill_gauss(lane, want_E, w.U, w.gret, w.gcache, w.E, w.ok);
+  router_bar();
   w.have_E = want_E;
-  __syncwarp();
 }
 
 __device__ __forceinline__ double win_double(NpWindow& w) {
@@ -316,7 +334,11 @@ __device__ __forceinline__ double win_gauss(NpWindow& w) {
 }
 
 // rk_standard_gamma of the legacy generator, reading the stream through the window (same arithmetic as np_std_gamma)
-__device__ double win_std_gamma(NpWindow& w, double shape) {
+// c = 1/sqrt(9 (shape - 1/3)) of the Marsaglia-Tsang loop, tabulated per arm when c_tab >= 0 (it only changes when the
+// arm receives feedback); a negative c_tab means "compute here"
+__device__ __forceinline__ double gamma_c(double shape) { return shape > 1.0 ? 1.0 / sqrt(9 * (shape - 1.0 / 3.0)) : 0.0; }
+
+__device__ __forceinline__ double win_std_gamma(NpWindow& w, double shape, double c_tab) {
   if (shape == 1.0) return win_exponential(w);
   if (shape == 0.0) return 0.0;
   if (shape < 1.0) {
@@ -333,7 +355,7 @@ __device__ double win_std_gamma(NpWindow& w, double shape) {
       }
     }
   }
-  const double b = shape - 1.0 / 3.0, c = 1.0 / sqrt(9 * b);
+  const double b = shape - 1.0 / 3.0, c = c_tab >= 0.0 ? c_tab : 1.0 / sqrt(9 * b);
   for (;;) {
     double x, v;
     do {
@@ -350,28 +372,33 @@ __device__ double win_std_gamma(NpWindow& w, double shape) {
   }
 }
 
-__device__ double win_beta(NpWindow& w, double a, double b) {
+// rk_beta: the variate is num / den (the division is left to the caller, which does all arms at once)
+__device__ __forceinline__ void win_beta(NpWindow& w, double a, double b, double ca, double cb, double* num, double* den) {
+  *den = 1.0;
+  *num = 0.0;
   if (a <= 1.0 && b <= 1.0) {
     for (;;) {
       const double u = win_double(w), v = win_double(w);
-      if (w.fail) return 0.0;
+      if (w.fail) return;
       const double x = pow(u, 1.0 / a), y = pow(v, 1.0 / b);
       const double xpy = __dadd_rn(x, y);
       if (xpy <= 1.0 && __dadd_rn(u, v) > 0.0) {
-        if (xpy > 0) return x / xpy;
+        if (xpy > 0) { *num = x; *den = xpy; return; }
         double lx = log(u) / a, ly = log(v) / b;
         const double lm = lx > ly ? lx : ly;
         lx -= lm; ly -= lm;
-        return exp(lx - log(__dadd_rn(exp(lx), exp(ly))));
+        *num = exp(lx - log(__dadd_rn(exp(lx), exp(ly))));
+        return;
       }
     }
   }
-  const double ga = win_std_gamma(w, a), gb = win_std_gamma(w, b);
-  return ga / __dadd_rn(ga, gb);
+  const double ga = win_std_gamma(w, a, ca), gb = win_std_gamma(w, b, cb);
+  *num = ga;
+  *den = __dadd_rn(ga, gb);
 }
 
 // T calls.  kind 0 = epsilon-greedy, 1 = Thompson.  reward_mode -1: route only.
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(kRouterThreads)
 router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon, long long T,
                   const long long* __restrict__ rows, const float* __restrict__ reward,
                   const float* __restrict__ arm_p, int reward_mode, int* __restrict__ decisions, int forced_arm,
@@ -379,8 +406,25 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
   __shared__ uint32_t s_py[MT_N], s_np[MT_N], s_np2[MT_N];
   __shared__ double s_U[kWinD + 2], s_gret[kWinD], s_gcache[kWinD], s_E[kWinD];
   __shared__ uint8_t s_ok[kWinD];
+  constexpr int kTabArms = 128;  // arms with tabulated gamma constants and a parallel division (beyond: inline)
+  __shared__ double s_ca[kTabArms], s_cb[kTabArms], s_num[kTabArms], s_den[kTabArms];
   __shared__ long long s_succ[kMaxArms], s_tries[kMaxArms];
   __shared__ double s_val[kMaxArms];
+  __shared__ WinCmd s_cmd;
+  if (threadIdx.x >= 32) {
+    // helper warps: table fills on command until warp 0 says exit
+    for (;;) {
+      router_bar();
+      const WinCmd c = s_cmd;
+      if (c.exit) return;
+      const uint32_t* b0 = c.cur ? s_np2 : s_np;
+      const uint32_t* b1 = c.cur ? s_np : s_np2;
+      win_fill_uniforms(threadIdx.x, c.p, b0, b1, s_U);
+      router_bar();
+      win_fill_gauss(threadIdx.x, c.want_E != 0, s_U, s_gret, s_gcache, s_E, s_ok);
+      router_bar();
+    }
+  }
   const int lane = threadIdx.x;
   for (int i = lane; i < MT_N; i += 32) { s_py[i] = st->py.mt[i]; s_np[i] = st->np.mt[i]; }
   for (int j = lane; j < n; j += 32) {
@@ -391,9 +435,15 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
   DevMt py{s_py, st->py.pos, 0, 0.0};
   DevMt np{s_np, st->np.pos, st->np.has_gauss, st->np.gauss};
   int best = st->best;
+  const bool tab = kind == 1 && n <= kTabArms;
+  if (tab)
+    for (int j = lane; j < n; j += 32) {
+      s_ca[j] = gamma_c((double)(1 + s_succ[j]));
+      s_cb[j] = gamma_c((double)(1 + s_tries[j] - s_succ[j]));
+    }
   __syncwarp();
   // Thompson: the NumPy stream is read through a window (committed position = np.pos at entry)
-  NpWindow win{{s_np, s_np2}, 0, 0, np.pos, 0, np.has_gauss, np.gauss, 0, s_U, s_gret, s_gcache, s_E, s_ok, 0};
+  NpWindow win{s_np, s_np2, 0, 0, np.pos, 0, np.has_gauss, np.gauss, 0, s_U, s_gret, s_gcache, s_E, s_ok, 0};
   const bool windowed = kind == 1 && forced_arm < 0;
   // room one beta draw may need: two gammas, each a few doubles per trial; a refill is forced below this margin
   constexpr int kArmMargin = 48;
@@ -418,12 +468,28 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
       unit = __any_sync(0xffffffffu, unit);
       for (int j = 0; j < n; ++j) {  // ThompsonSampling.py:81-82, arm order; np.argmax = first maximum
         if (!win_built || kWinD - win.head < kArmMargin) {
-          np_window_build(win, unit);
+          np_window_build(win, unit, &s_cmd);
           win_built = 1;
         }
         const double a = (double)(1 + s_succ[j]), b = (double)(1 + s_tries[j] - s_succ[j]);
-        const double v = win_beta(win, a, b);
-        if (j == 0 || v > top) { top = v; arm = j; }
+        double num, den;
+        win_beta(win, a, b, tab ? s_ca[j] : -1.0, tab ? s_cb[j] : -1.0, &num, &den);
+        if (tab) {
+          if (lane == 0) { s_num[j] = num; s_den[j] = den; }
+        } else {
+          const double v = num / den;
+          if (j == 0 || v > top) { top = v; arm = j; }
+        }
+      }
+      if (tab) {
+        // the n divisions in parallel, then the same first-maximum scan
+        __syncwarp();
+        for (int j = lane; j < n; j += 32) s_num[j] = s_num[j] / s_den[j];
+        __syncwarp();
+        for (int j = 0; j < n; ++j) {
+          const double v = s_num[j];
+          if (j == 0 || v > top) { top = v; arm = j; }
+        }
       }
       if (win.fail) {
         // one beta draw needed more than kArmMargin doubles (probability ~1e-20): this and the remaining calls are
@@ -446,6 +512,10 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
       s_succ[arm] += ns;
       s_tries[arm] += nrows;
       if (kind == 0) s_val[arm] = (double)s_succ[arm] / (double)s_tries[arm];  // L118-119
+      if (tab) {
+        s_ca[arm] = gamma_c((double)(1 + s_succ[arm]));
+        s_cb[arm] = gamma_c((double)(1 + s_tries[arm] - s_succ[arm]));
+      }
     }
     __syncwarp();
     if (kind == 0) {
@@ -475,14 +545,17 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
     }
   }
   __syncwarp();
+  if (lane == 0) s_cmd.exit = 1;
+  __syncwarp();
+  router_bar();  // helper warps leave
   const uint32_t* np_blk = s_np;
   if (windowed && win_built) {
     // commit the consumed part of the window: the state a draw-by-draw generator would be in
     int p = win.pos + 2 * win.head;
     if (p > MT_N) {
       if (!win.next_valid) {
-        for (int i = lane; i < MT_N; i += 32) win.blk[win.cur ^ 1][i] = win.blk[win.cur][i];
-        mt_regenerate(win.blk[win.cur ^ 1]);
+        for (int i = lane; i < MT_N; i += 32) win_blk(win, win.cur ^ 1)[i] = win_blk(win, win.cur)[i];
+        mt_regenerate(win_blk(win, win.cur ^ 1));
       }
       win.cur ^= 1;
       p -= MT_N;
@@ -490,7 +563,7 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
     np.pos = p;
     np.has_gauss = win.has_gauss;
     np.gauss = win.gauss;
-    np_blk = win.blk[win.cur];
+    np_blk = win_blk(win, win.cur);
     __syncwarp();
   }
   for (int i = lane; i < MT_N; i += 32) { st->py.mt[i] = s_py[i]; st->np.mt[i] = np_blk[i]; }
@@ -583,7 +656,7 @@ extern "C" int32_t sb_router_run(sb_router_t* h, int64_t T, const int64_t* d_row
   SB_REQUIRE(reward_mode != SB_REWARD_BERNOULLI || d_arm_p, SB_ERR_INVALID, "sb_router_run: arm probabilities required");
   SB_REQUIRE(!(h->kind == SB_ROUTER_EPSILON_GREEDY && h->n < 2), SB_ERR_INVALID,
              "epsilon-greedy needs >= 2 branches to explore (reference raises IndexError on random.choice([]))");
-  router_run_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, (long long)T,
+  router_run_kernel<<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, (long long)T,
                                                        (const long long*)d_rows_per_call, d_reward, d_arm_p,
                                                        reward_mode, d_decisions, -1, 0.0, 0);
   SB_LAUNCH_CHECK();
@@ -594,7 +667,7 @@ extern "C" int32_t sb_router_feedback(sb_router_t* h, int32_t arm, int64_t rows,
   SB_REQUIRE(h && arm >= 0 && arm < h->n, SB_ERR_INVALID, "sb_router_feedback: routing %d outside 0..%d", arm,
              h ? h->n - 1 : 0);
   SB_REQUIRE(rows >= 1, SB_ERR_INVALID, "sb_router_feedback: rows must be >= 1 (reference divides by tries)");
-  router_run_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, 1, nullptr, nullptr,
+  router_run_kernel<<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, 1, nullptr, nullptr,
                                                        nullptr, 0, nullptr, arm, reward, (long long)rows);
   SB_LAUNCH_CHECK();
   return SB_OK;
