@@ -108,7 +108,7 @@ sub_project(const TIn* __restrict__ recs, size_t rec_stride, int nitems, int d, 
 // adds up the totals of the chunks before it (a few hundred at most) and rewrites its 32 rows.
 constexpr int kScanChunk = 32;
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 sub_scan_totals(const double* __restrict__ subproj, int nsub, int KQ, double* __restrict__ chunk_tot) {
   const int chunk = blockIdx.x;
   const int s0 = chunk * kScanChunk, s1 = min(nsub, s0 + kScanChunk);
@@ -120,7 +120,7 @@ sub_scan_totals(const double* __restrict__ subproj, int nsub, int KQ, double* __
 }
 
 // exclusive scan over the chunk totals, in place, starting from this rank's offset (one block, a thread per component)
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 sub_scan_chunks(double* __restrict__ chunk_tot, int nchunk, int KQ, const double* __restrict__ rank_off) {
   for (int comp = threadIdx.x; comp < KQ; comp += blockDim.x) {
     double run = rank_off[comp];
@@ -133,7 +133,7 @@ sub_scan_chunks(double* __restrict__ chunk_tot, int nchunk, int KQ, const double
   }
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 sub_scan_apply(double* __restrict__ subproj, int nsub, int KQ, const double* __restrict__ chunk_pre) {
   const int chunk = blockIdx.x, nchunk = gridDim.x;
   const int s0 = chunk * kScanChunk, s1 = min(nsub, s0 + kScanChunk);
@@ -1474,6 +1474,9 @@ project_cov(const double* __restrict__ C0, const double* __restrict__ V, int d, 
   }
 }
 
+// one thread per projected statistic (KQ = KP + KP^2), whole warps
+inline int scan_threads(int KQ) { return KQ >= 1024 ? 1024 : ((KQ + 31) & ~31); }
+
 template <int KP>
 int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream_t st) {
   const int d = h->d, nsub = h->lay.nsub;
@@ -1501,11 +1504,11 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
   sub_project<float><<<grid, 256, sp_smem, st>>>(ws.partials, PS, nsub, d, KP, h->d_Vf, ws.subproj);
   SB_LAUNCH_CHECK();
   const int nchunk = (int)ceil_div(nsub, kScanChunk);
-  sub_scan_totals<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
+  sub_scan_totals<<<nchunk, scan_threads(KQ), 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
   SB_LAUNCH_CHECK();
-  sub_scan_chunks<<<1, 256, 0, st>>>(ws.chunk_tot, nchunk, KQ, rank_proj);
+  sub_scan_chunks<<<1, scan_threads(KQ), 0, st>>>(ws.chunk_tot, nchunk, KQ, rank_proj);
   SB_LAUNCH_CHECK();
-  sub_scan_apply<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
+  sub_scan_apply<<<nchunk, scan_threads(KQ), 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
   SB_LAUNCH_CHECK();
   sub_start<KP><<<(int)ceil_div(nsub, 4), 128, 0, st>>>(ws.subproj, h->d_PC0, h->lay, h->k, (long long)h->n_eff,
                                                        (long long)h->row0, ws.sub_P, ws.sub_Z, ws.sub_flags);
@@ -1549,11 +1552,11 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
     if (h->profile) cudaEventRecord(h->ev[7], st);
     constexpr int KQ = KP + KP * KP;
     const int nchunk = (int)ceil_div(nsub, kScanChunk);
-    sub_scan_totals<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
+    sub_scan_totals<<<nchunk, scan_threads(KQ), 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
     SB_LAUNCH_CHECK();
-    sub_scan_chunks<<<1, 256, 0, st>>>(ws.chunk_tot, nchunk, KQ, ws.rank_proj);
+    sub_scan_chunks<<<1, scan_threads(KQ), 0, st>>>(ws.chunk_tot, nchunk, KQ, ws.rank_proj);
     SB_LAUNCH_CHECK();
-    sub_scan_apply<<<nchunk, 256, 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
+    sub_scan_apply<<<nchunk, scan_threads(KQ), 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
     SB_LAUNCH_CHECK();
     sub_start<KP><<<(int)ceil_div(nsub, 4), 128, 0, st>>>(ws.subproj, h->d_PC0, L, h->k, (long long)h->n_eff,
                                                          (long long)h->row0, ws.sub_P, ws.sub_Z, ws.sub_flags);
