@@ -9,7 +9,7 @@
 //   - NumPy legacy     : init_genrand seeding, masked-rejection bounded integers (tie break, np.random.choice),
 //                        legacy beta = Johnk (a,b <= 1) or two Marsaglia-Tsang gammas fed by the cached polar
 //                        Gaussian (np.random.beta)
-// The bandit is sequential in time (route_t depends on feedback_{t-1}); this is a latency kernel, one warp, all
+// The bandit is sequential in time (route_t depends on feedback_{t-1}); this is a latency kernel: warp 0 runs it, all
 // lanes executing the same instruction stream (the generator state lives in shared memory and is advanced
 // uniformly), lanes = arms for the tie-break scan.  It has no roofline; bench.py reports calls/s.
 #include <string.h>
@@ -232,6 +232,7 @@ struct NpWindow {
   int fail;          // a single beta draw ran past the window (probability ~1e-20): reported to the host
   double *U, *gret, *gcache, *E;
   uint8_t* ok;
+  short* nok;        // nok[i] = first position j >= i, j = i mod 2, whose polar attempt succeeds (kWinD: none in reach)
   int have_E;
 };
 
@@ -276,6 +277,14 @@ __device__ __forceinline__ void win_fill_gauss(int tid, bool want_E, const doubl
   }
 }
 
+__device__ __forceinline__ void win_fill_next_ok(int tid, const uint8_t* ok, short* nok) {
+  for (int i = tid; i < kWinD; i += kRouterThreads) {
+    int j = i;
+    while (j < kWinD && !ok[j]) j += 2;
+    nok[i] = (short)(j < kWinD ? j : kWinD);
+  }
+}
+
 // move the committed position to the first unconsumed word and fill the tables from there (called by warp 0)
 __device__ __forceinline__ void np_window_build(NpWindow& w, bool want_E, WinCmd* cmd) {
   const int lane = threadIdx.x & 31;
@@ -304,6 +313,8 @@ __device__ __forceinline__ void np_window_build(NpWindow& w, bool want_E, WinCmd
   win_fill_uniforms(lane, p, win_blk(w, w.cur), win_blk(w, w.cur ^ 1), w.U);
   router_bar();
   win_fill_gauss(lane, want_E, w.U, w.gret, w.gcache, w.E, w.ok);
+  router_bar();
+  win_fill_next_ok(lane, w.ok, w.nok);
   router_bar();
   w.have_E = want_E;
 }
@@ -406,8 +417,10 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
   __shared__ uint32_t s_py[MT_N], s_np[MT_N], s_np2[MT_N];
   __shared__ double s_U[kWinD + 2], s_gret[kWinD], s_gcache[kWinD], s_E[kWinD];
   __shared__ uint8_t s_ok[kWinD];
+  __shared__ short s_nok[kWinD];
   constexpr int kTabArms = 128;  // arms with tabulated gamma constants and a parallel division (beyond: inline)
   __shared__ double s_ca[kTabArms], s_cb[kTabArms], s_num[kTabArms], s_den[kTabArms];
+  __shared__ uint8_t s_kind[kTabArms];  // bit 0: a == 1, bit 1: b == 1 (unit shapes draw an exponential, no Gaussian)
   __shared__ long long s_succ[kMaxArms], s_tries[kMaxArms];
   __shared__ double s_val[kMaxArms];
   __shared__ WinCmd s_cmd;
@@ -422,6 +435,8 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
       win_fill_uniforms(threadIdx.x, c.p, b0, b1, s_U);
       router_bar();
       win_fill_gauss(threadIdx.x, c.want_E != 0, s_U, s_gret, s_gcache, s_E, s_ok);
+      router_bar();
+      win_fill_next_ok(threadIdx.x, s_ok, s_nok);
       router_bar();
     }
   }
@@ -440,10 +455,11 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
     for (int j = lane; j < n; j += 32) {
       s_ca[j] = gamma_c((double)(1 + s_succ[j]));
       s_cb[j] = gamma_c((double)(1 + s_tries[j] - s_succ[j]));
+      s_kind[j] = (uint8_t)((s_succ[j] == 0 ? 1 : 0) | (s_tries[j] == s_succ[j] ? 2 : 0));
     }
   __syncwarp();
   // Thompson: the NumPy stream is read through a window (committed position = np.pos at entry)
-  NpWindow win{s_np, s_np2, 0, 0, np.pos, 0, np.has_gauss, np.gauss, 0, s_U, s_gret, s_gcache, s_E, s_ok, 0};
+  NpWindow win{s_np, s_np2, 0, 0, np.pos, 0, np.has_gauss, np.gauss, 0, s_U, s_gret, s_gcache, s_E, s_ok, s_nok, 0};
   const bool windowed = kind == 1 && forced_arm < 0;
   // room one beta draw may need: two gammas, each a few doubles per trial; a refill is forced below this margin
   constexpr int kArmMargin = 48;
@@ -466,22 +482,100 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
       bool unit = false;
       for (int j = lane; j < n; j += 32) unit |= s_succ[j] == 0 || s_tries[j] == s_succ[j];
       unit = __any_sync(0xffffffffu, unit);
-      for (int j = 0; j < n; ++j) {  // ThompsonSampling.py:81-82, arm order; np.argmax = first maximum
-        if (!win_built || kWinD - win.head < kArmMargin) {
-          np_window_build(win, unit, &s_cmd);
-          win_built = 1;
+      if (tab) {
+        // Arms as lanes.  The draws of one route read the stream one after the other, but nearly always in a pattern
+        // that the tables give away: a gamma with shape > 1 takes the cached Gaussian or else the first successful polar
+        // pair at or after its position (nok[]) and one uniform (the squeeze test accepts ~97 %), a unit shape takes
+        // one uniform, two unit shapes (Johnk) take pairs of uniforms until their sum is <= 1.  The warp follows that
+        // pattern arm by arm (cheap, table look-ups only) and lane l latches the state PREDICTED for arm done + l;
+        // each lane then draws its beta from there on a private copy of the window state, and the warp accepts the
+        // longest prefix of lanes whose assumed start state equals the actual end state of the lane before (position,
+        // cached-Gaussian flag and value).  Everything accepted is exactly what the sequential walk would have drawn.
+        int done = 0;
+        while (done < n) {
+          if (!win_built || kWinD - win.head < kArmMargin) {
+            np_window_build(win, unit, &s_cmd);
+            win_built = 1;
+          }
+          const int D = min(n - done, 32);
+          int p = win.head, f = win.has_gauss, gq = -1;   // lane 0: the actual state
+          {
+            int cp = p, cf = f, cq = -1;  // the chase, identical in every lane
+            for (int it = 1; it < D; ++it) {
+              const int kd = s_kind[done + it - 1];
+              if (kd == 3) {
+                int tries = 0;
+                while (cp + 1 < kWinD && tries < 16 && !(__dadd_rn(s_U[cp], s_U[cp + 1]) <= 1.0)) { cp += 2; ++tries; }
+                cp += 2;
+              } else if (cf) {
+                if (kd == 0) {
+                  const int q = cp + 1 < kWinD ? (int)s_nok[cp + 1] : kWinD;
+                  cp = q + 3;
+                  cq = q;
+                } else {
+                  cp += 2;
+                  cf = 0;
+                }
+              } else {
+                const int at = kd == 1 ? cp + 1 : cp;
+                const int q = at < kWinD ? (int)s_nok[at] : kWinD;
+                cp = kd == 1 ? q + 3 : q + 4;
+                if (kd != 0) { cf = 1; cq = q; }
+              }
+              if (cp > kWinD) cp = kWinD;
+              if (lane == it) { p = cp; f = cf; gq = cq; }
+            }
+          }
+          bool valid = lane < D && p <= kWinD - kArmMargin;
+          double g_in = win.gauss;
+          if (lane > 0) {
+            g_in = 0.0;
+            if (f) {  // the value the arms before leave in the cache: the other half of the last polar pair
+              valid = valid && gq >= 0 && gq < kWinD && s_ok[gq];
+              if (valid) g_in = s_gcache[gq];
+            }
+          }
+          const int flag0 = f;
+          NpWindow lw = win;
+          lw.head = p;
+          lw.has_gauss = flag0;
+          lw.gauss = g_in;
+          lw.fail = 0;
+          const int j = done + lane;
+          double num = 0.0, den = 1.0;
+          if (valid) {
+            const double a = (double)(1 + s_succ[j]), b = (double)(1 + s_tries[j] - s_succ[j]);
+            win_beta(lw, a, b, s_ca[j], s_cb[j], &num, &den);
+          }
+          const int e_head = lw.head, e_flag = lw.has_gauss;
+          const long long e_bits = __double_as_longlong(lw.gauss);
+          const int pe_head = __shfl_up_sync(0xffffffffu, e_head, 1), pe_flag = __shfl_up_sync(0xffffffffu, e_flag, 1);
+          const long long pe_bits = __shfl_up_sync(0xffffffffu, e_bits, 1);
+          const bool okl = valid && !lw.fail &&
+                           (lane == 0 || (pe_head == p && pe_flag == flag0 && (!flag0 || pe_bits == __double_as_longlong(g_in))));
+          const unsigned bal = __ballot_sync(0xffffffffu, okl);
+          const int k = bal == 0xffffffffu ? 32 : __ffs((int)~bal) - 1;  // accepted lanes: 0 .. k-1
+          if (k == 0) { win.fail = 1; break; }  // the first lane itself ran out of window
+          if (lane < k) { s_num[j] = num; s_den[j] = den; }
+          win.head = __shfl_sync(0xffffffffu, e_head, k - 1);
+          win.has_gauss = __shfl_sync(0xffffffffu, e_flag, k - 1);
+          win.gauss = __longlong_as_double(__shfl_sync(0xffffffffu, e_bits, k - 1));
+          done += k;
         }
-        const double a = (double)(1 + s_succ[j]), b = (double)(1 + s_tries[j] - s_succ[j]);
-        double num, den;
-        win_beta(win, a, b, tab ? s_ca[j] : -1.0, tab ? s_cb[j] : -1.0, &num, &den);
-        if (tab) {
-          if (lane == 0) { s_num[j] = num; s_den[j] = den; }
-        } else {
+      } else {
+        for (int j = 0; j < n; ++j) {  // ThompsonSampling.py:81-82, arm order; np.argmax = first maximum
+          if (!win_built || kWinD - win.head < kArmMargin) {
+            np_window_build(win, unit, &s_cmd);
+            win_built = 1;
+          }
+          const double a = (double)(1 + s_succ[j]), b = (double)(1 + s_tries[j] - s_succ[j]);
+          double num, den;
+          win_beta(win, a, b, -1.0, -1.0, &num, &den);
           const double v = num / den;
           if (j == 0 || v > top) { top = v; arm = j; }
         }
       }
-      if (tab) {
+      if (tab && !win.fail) {
         // the n divisions in parallel, then the same first-maximum scan
         __syncwarp();
         for (int j = lane; j < n; j += 32) s_num[j] = s_num[j] / s_den[j];
@@ -515,6 +609,7 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
       if (tab) {
         s_ca[arm] = gamma_c((double)(1 + s_succ[arm]));
         s_cb[arm] = gamma_c((double)(1 + s_tries[arm] - s_succ[arm]));
+        s_kind[arm] = (uint8_t)((s_succ[arm] == 0 ? 1 : 0) | (s_tries[arm] == s_succ[arm] ? 2 : 0));
       }
     }
     __syncwarp();
