@@ -85,3 +85,23 @@ def test_statistics_like_reference_test():
     _cabi.check(_cabi.lib().sb_router_run(r._handle(), 100000, None, None, None, -1, dec.data_ptr(), r._stream()))
     frac = float((dec == first).float().mean().item())
     assert np.isclose(frac, 0.9, atol=0, rtol=0.01)
+
+
+@pytest.mark.parametrize("n,T,chunks", [(200, 600, (600,)), (32, 5000, (1, 7, 992, 4000)), (5, 3000, (1500, 1, 1499)),
+                                        (64, 3000, (3000,)), (128, 1500, (700, 800))])
+def test_thompson_window_paths_against_c_oracle(n, T, chunks):
+    """The look-ahead window of the Thompson kernel: more arms than lanes, more than the tabulated 128 (draw-by-draw
+    through the window), and launches that end anywhere inside a window (the committed generator state must be the one
+    a draw-by-draw generator would have)."""
+    p, u = synth.router_rewards(T, n)
+    ref, st = R.run_batched(1, n, 0.1, 3, 0, T, reward=u, reward_mode=R.REWARD_BERNOULLI, arm_p=p)
+    r = ThompsonSamplingB200(n_branches=n, seed=3)
+    got, off = [], 0
+    for c in chunks:
+        got.append(r.run_batched(c, u[off:off + c], reward_mode=_cabi.SB_REWARD_BERNOULLI, arm_p=p).cpu().numpy())
+        off += c
+        if off == chunks[0]:
+            r = pickle.loads(pickle.dumps(r))  # state round trip in the middle of the stream
+    dec = np.concatenate(got)
+    assert np.array_equal(dec, ref), "first mismatch at call %d" % int(np.flatnonzero(dec != ref)[0])
+    assert r.branch_success == st[:n].tolist() and r.branch_tries == st[n:2 * n].tolist()
