@@ -79,6 +79,38 @@ __global__ void __launch_bounds__(256) standardise_kernel(const float* __restric
   }
 }
 
+// contiguous rows, cols % 4 == 0: the matrix as a flat array of float4; the column of a vector advances by a fixed step
+// per grid stride, so no division in the loop; four independent vectors in flight per thread
+__global__ void __launch_bounds__(256) standardise_vec4(const float4* __restrict__ in, int64_t n_vec, int q,
+                                                         const float4* __restrict__ mu, const float4* __restrict__ inv_sigma,
+                                                         float4* __restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int c = (int)(i % q);
+  const int step = (int)(stride % q);
+  constexpr int U = 4;
+  for (; i < n_vec; i += U * stride) {
+    float4 v[U];
+    int cc[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      cc[u] = c;
+      c += step;
+      if (c >= q) c -= q;
+      const int64_t k = i + u * stride;
+      if (k < n_vec) v[u] = sb::ldg_stream_f4(in + k);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t k = i + u * stride;
+      if (k >= n_vec) break;
+      const float4 m = __ldg(mu + cc[u]), s = __ldg(inv_sigma + cc[u]);
+      sb::stg_stream_f4(out + k, make_float4((v[u].x - m.x) * s.x, (v[u].y - m.y) * s.y, (v[u].z - m.z) * s.z,
+                                             (v[u].w - m.w) * s.w));
+    }
+  }
+}
+
 }  // namespace
 
 extern "C" int32_t sb_combiner_mean(const float* const* h_inputs, int32_t n_children, int64_t n_elems, float* d_out,
@@ -125,6 +157,17 @@ extern "C" int32_t sb_standardise(const float* d_in, int64_t rows, int64_t cols,
   SB_REQUIRE(d_mu && d_inv_sigma, SB_ERR_INVALID, "sb_standardise: mu/inv_sigma required");
   if (rows == 0) return SB_OK;
   SB_REQUIRE(d_in && d_out, SB_ERR_INVALID, "sb_standardise: null matrix");
+  const bool vec = cols % 4 == 0 && ld_in == cols && ld_out == cols &&
+                   (((uintptr_t)d_in | (uintptr_t)d_out | (uintptr_t)d_mu | (uintptr_t)d_inv_sigma) & 15) == 0;
+  if (vec) {
+    const int64_t n_vec = rows * cols / 4;
+    int64_t w4 = sb::ceil_div(n_vec, 256 * 4);
+    int g4 = (int)(w4 < (int64_t)sb::kNumSMs * 8 ? (w4 > 0 ? w4 : 1) : (int64_t)sb::kNumSMs * 8);
+    standardise_vec4<<<g4, 256, 0, (cudaStream_t)stream>>>((const float4*)d_in, n_vec, (int)(cols / 4), (const float4*)d_mu,
+                                                          (const float4*)d_inv_sigma, (float4*)d_out);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+  }
   int64_t want = sb::ceil_div(rows * cols, 256 * 4);
   int grid = (int)(want < (int64_t)sb::kNumSMs * 8 ? (want > 0 ? want : 1) : (int64_t)sb::kNumSMs * 8);
   standardise_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_in, rows, (int)cols, ld_in, d_mu, d_inv_sigma, d_out,

@@ -48,10 +48,11 @@ def test_mnist_combiner_fixture(golden_dir):
     assert np.max(np.abs(out - g["out"]) / np.abs(g["out"])) <= 1e-6
 
 
-def test_standardise_matches_oracle():
+@pytest.mark.parametrize("shape", [(513, 37), (1000, 256), (3, 4), (70001, 64)])
+def test_standardise_matches_oracle(shape):
     rs = np.random.RandomState(0)
-    X = rs.randn(513, 37).astype(np.float32)
-    mu, sigma = rs.randn(37), rs.rand(37) + 0.1
+    X = rs.randn(*shape).astype(np.float32)  # 37 columns: scalar kernel; multiples of 4: the float4 kernel
+    mu, sigma = rs.randn(shape[1]), rs.rand(shape[1]) + 0.1
     out = StandardiseB200(mu, sigma).transform_input(X, None)
     ref = standardise(X, mu.astype(np.float32), sigma)
     assert np.max(np.abs(out - ref) / np.maximum(np.abs(ref), 1e-3)) < 1e-5
