@@ -138,6 +138,14 @@ int32_t sb_maha_abort_batch(sb_maha_t* h);
 int32_t sb_maha_batch(sb_maha_t* h, const float* d_X, int64_t rows, int64_t ld, float* d_score, int32_t* d_flag,
                       void* d_ws, uint64_t ws_bytes, uintptr_t stream);
 
+/* Fuses the standardise transformer (CoreVAE.py:128, (X - mu) / (sigma + 1e-10); sb_standardise above) into the
+ * detector: with d_mu / d_inv_sigma set (fp32[d] device vectors owned by the caller, 16-byte aligned, kept alive while
+ * set; NULL, NULL switches it off) every batch is scored as if sb_standardise had been applied to it first - the same
+ * two fp32 roundings per value, so the results agree with the two-step graph to the detector's own run-to-run spread
+ * (a few 1e-7 relative in the scores, equal flags) - without the 8*d B/row of the separate pass.  Only on the tensor-core path (d = 64, 128, 256, n_components <= 16, aligned rows);
+ * other shapes report SB_ERR_INVALID at sb_maha_pass1_stats. */
+int32_t sb_maha_set_input_transform(sb_maha_t* h, const float* d_mu, const float* d_inv_sigma);
+
 /* Pass-1 statistics without any workspace: count, sum and Gram of (x - shift) over `rows` rows of an fp32 device
  * matrix into d_stats_out (1 + d + d*d doubles, the record layout of sb_maha_pass1_stats).  Has no counterpart in
  * the reference (which never leaves the host).  It exists for callers that cannot allocate device memory: bindings

@@ -39,6 +39,7 @@ SIGNATURES = {
     "sb_feedback_update": (c_int32, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, _uintptr]),
     "sb_maha_create": (c_int32, [_pp, c_int32, c_int32, c_double, c_double, c_int64, c_int64]),
     "sb_maha_destroy": (c_int32, [c_void_p]),
+    "sb_maha_set_input_transform": (c_int32, [c_void_p, c_void_p, c_void_p]),
     "sb_maha_workspace_bytes": (c_int32, [c_void_p, c_int64, POINTER(c_uint64)]),
     "sb_maha_stats_len": (c_int64, [c_void_p]),
     "sb_maha_pass1_stats": (c_int32, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_uint64, c_void_p, _uintptr]),

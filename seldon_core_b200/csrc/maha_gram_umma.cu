@@ -100,17 +100,21 @@ __host__ __device__ constexpr int umma_chunk_rows(int D) { return 8192 / D; }
 __host__ __device__ constexpr size_t umma_smem_bytes(int D, int terms) {
   return (size_t)umma_tile_stages(D) * (terms == 3 ? 2 : 1) * umma_chunk_rows(D) * D * 4 +
          (umma_raw_staged(D) ? (size_t)kRawStages * umma_chunk_rows(D) * D * 4 : 0) +
-         (D > 128 ? (size_t)3 * D * 4 : 0) /* mean and clip bounds when they do not fit in registers */ + 1024 /* alignment slack */;
+         (D > 128 ? (size_t)5 * D * 4 : 0) /* mean, clip bounds, input transform when they do not fit in registers */ +
+         1024 /* alignment slack */;
 }
 
 constexpr int kUmmaThreads = 512;            // producer threads (16 warps); one more warp issues the MMAs
 constexpr int kUmmaBlock = kUmmaThreads + 32;
 __host__ __device__ constexpr int umma_block(int D) { return kUmmaBlock + (umma_raw_staged(D) ? 32 : 0); }  // + loader warp
 
-template <int D, bool CLIP, int TERMS>
+// STD: the rows are standardised on load, x' = (x - in_mu) * in_is per feature with the two roundings of the stand-alone
+// standardise kernel (combiner.cu), so that fusing the transformer into the detector feeds it the same values.
+template <int D, bool CLIP, int TERMS, bool STD>
 __global__ void __launch_bounds__(umma_block(D), 1)
 pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const float* __restrict__ mean_f,
-                const float* __restrict__ lo_f, const float* __restrict__ hi_f, float* __restrict__ partials) {
+                const float* __restrict__ lo_f, const float* __restrict__ hi_f, const float* __restrict__ in_mu,
+                const float* __restrict__ in_is, float* __restrict__ partials) {
   constexpr int PS = D + D * D;
   constexpr int NSLAB = D / 32;                 // 128-byte feature slabs per row
   constexpr uint32_t LBO = 512;                 // between feature slabs of one 4-row atom
@@ -155,6 +159,8 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
       ms[f] = mean_f[f];
       los[f] = CLIP ? lo_f[f] : 0.f;
       his[f] = CLIP ? hi_f[f] : 0.f;
+      his[D + f] = STD ? in_mu[f] : 0.f;
+      his[2 * D + f] = STD ? in_is[f] : 0.f;
     }
   }
   if (tid == 0) {
@@ -276,8 +282,16 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   const uint32_t off0 = (uint32_t)(krow >> 2) * SBO + (uint32_t)(piece0 >> 3) * LBO + (uint32_t)(krow & 3) * 128u +
                         ((((b0 >> 5) ^ (uint32_t)(krow & 3)) << 5) | (b0 & 31u));
   float4 m_r[HOIST ? NPIECE : 1], l_r[HOIST ? NPIECE : 1], h_r[HOIST ? NPIECE : 1];
+  float4 su_r[HOIST && STD ? NPIECE : 1], si_r[HOIST && STD ? NPIECE : 1];
   if (HOIST) {
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (STD) {
+#pragma unroll
+      for (int i = 0; i < NPIECE; ++i) {
+        su_r[i] = *reinterpret_cast<const float4*>(in_mu + 4 * (piece0 + 16 * i));
+        si_r[i] = *reinterpret_cast<const float4*>(in_is + 4 * (piece0 + 16 * i));
+      }
+    }
 #pragma unroll
     for (int i = 0; i < NPIECE; ++i) {
       m_r[i] = *reinterpret_cast<const float4*>(mean_f + 4 * (piece0 + 16 * i));
@@ -332,6 +346,18 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
               ll[0] = l4.x; ll[1] = l4.y; ll[2] = l4.z; ll[3] = l4.w;
               hh[0] = h4.x; hh[1] = h4.y; hh[2] = h4.z; hh[3] = h4.w;
             }
+          }
+          if (STD) {
+            float4 u4, s4;
+            if (HOIST) { u4 = su_r[i]; s4 = si_r[i]; }
+            else {
+              u4 = *reinterpret_cast<const float4*>(his + D + 4 * (piece0 + 16 * i));
+              s4 = *reinterpret_cast<const float4*>(his + 2 * D + 4 * (piece0 + 16 * i));
+            }
+            v[0] = __fmul_rn(__fsub_rn(v[0], u4.x), s4.x);
+            v[1] = __fmul_rn(__fsub_rn(v[1], u4.y), s4.y);
+            v[2] = __fmul_rn(__fsub_rn(v[2], u4.z), s4.z);
+            v[3] = __fmul_rn(__fsub_rn(v[3], u4.w), s4.w);
           }
           uint32_t hi4[4], lo4[4];
 #pragma unroll
@@ -502,11 +528,17 @@ template <int D>
 int launch_umma_d(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws, cudaStream_t st) {
   const SubLayout& L = h->lay;
   int grid = L.nsub < kNumSMs ? L.nsub : kNumSMs;
-#define SB_UMMA_LAUNCH(CLIPV, TERMSV)                                                                                   \
+#define SB_UMMA_LAUNCH2(CLIPV, TERMSV, STDV)                                                                            \
   do {                                                                                                                  \
     const size_t smem = umma_smem_bytes(D, TERMSV);                                                                     \
-    SB_CUDA(cudaFuncSetAttribute(pass1_gram_umma<D, CLIPV, TERMSV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    pass1_gram_umma<D, CLIPV, TERMSV><<<grid, umma_block(D), smem, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, ws.partials); \
+    SB_CUDA(cudaFuncSetAttribute(pass1_gram_umma<D, CLIPV, TERMSV, STDV>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                 (int)smem));                                                                           \
+    pass1_gram_umma<D, CLIPV, TERMSV, STDV><<<grid, umma_block(D), smem, st>>>(                                         \
+        X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_in_mu, h->d_in_is, ws.partials);                              \
+  } while (0)
+#define SB_UMMA_LAUNCH(CLIPV, TERMSV)                                                                                   \
+  do {                                                                                                                  \
+    if (h->d_in_mu) SB_UMMA_LAUNCH2(CLIPV, TERMSV, true); else SB_UMMA_LAUNCH2(CLIPV, TERMSV, false);                   \
   } while (0)
   if (h->use_clip) {
     if (h->gram_terms == 3) SB_UMMA_LAUNCH(true, 3); else SB_UMMA_LAUNCH(true, 1);
@@ -514,6 +546,7 @@ int launch_umma_d(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws
     if (h->gram_terms == 3) SB_UMMA_LAUNCH(false, 3); else SB_UMMA_LAUNCH(false, 1);
   }
 #undef SB_UMMA_LAUNCH
+#undef SB_UMMA_LAUNCH2
   return SB_OK;
 }
 

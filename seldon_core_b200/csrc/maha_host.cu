@@ -147,6 +147,18 @@ extern "C" int32_t sb_maha_workspace_bytes(const sb_maha_t* h, int64_t max_rows,
 
 extern "C" int64_t sb_maha_stats_len(const sb_maha_t* h) { return h ? 1 + (int64_t)h->d + (int64_t)h->d * h->d : 0; }
 
+extern "C" int32_t sb_maha_set_input_transform(sb_maha_t* h, const float* d_mu, const float* d_inv_sigma) {
+  SB_REQUIRE(h, SB_ERR_INVALID, "sb_maha_set_input_transform: null handle");
+  SB_REQUIRE((d_mu == nullptr) == (d_inv_sigma == nullptr), SB_ERR_INVALID,
+             "sb_maha_set_input_transform: mu and inv_sigma go together");
+  SB_REQUIRE(h->stage == 0, SB_ERR_STATE, "sb_maha_set_input_transform: a batch is in flight");
+  SB_REQUIRE(d_mu == nullptr || ((((uintptr_t)d_mu | (uintptr_t)d_inv_sigma) & 15) == 0), SB_ERR_INVALID,
+             "sb_maha_set_input_transform: the vectors must be 16-byte aligned");
+  h->d_in_mu = d_mu;
+  h->d_in_is = d_inv_sigma;
+  return SB_OK;
+}
+
 extern "C" int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t value) {
   SB_REQUIRE(h, SB_ERR_INVALID, "sb_maha_set_option: null handle");
   if (option == SB_OPT_GRAM_TERMS) {
@@ -184,6 +196,9 @@ extern "C" int32_t sb_maha_pass1_stats(sb_maha_t* h, const float* d_X, int64_t r
   h->split_pass2 = h->KP == 16 && (h->d == 64 || h->d == 128 || h->d == 256) && !h->force_generic &&
                    !h->fused_pass2 && (ld % 4 == 0) && (((uintptr_t)d_X & 15) == 0);
   h->lay2 = h->split_pass2 ? make_layout2(rows) : h->lay;
+  SB_REQUIRE(h->d_in_mu == nullptr || (h->split_pass2 && !h->legacy_mma), SB_ERR_INVALID,
+             "sb_maha_pass1_stats: the fused input transform needs the tensor-core path (d = 64, 128 or 256, "
+             "n_components <= 16, 16-byte aligned rows, no SB_OPT_FORCE_GENERIC / FUSED_PASS2 / LEGACY_MMA)");
   if ((rc = launch_pass1(h, d_X, ld, ws, st))) return rc;
   if ((rc = launch_reduce(h, ws, d_stats_out ? d_stats_out : ws.stats, st))) return rc;
   h->stage = 1;

@@ -234,7 +234,8 @@ __global__ void __launch_bounds__(32)
 score_slow(const float* __restrict__ X, int64_t ld, int d, int k, SubLayout lay, const double* __restrict__ mean,
            const double* __restrict__ lo, const double* __restrict__ hi, const double* __restrict__ V,
            const double* __restrict__ PC0, const double* __restrict__ subproj, const int32_t* __restrict__ sub_flags,
-           long long n_eff, long long row0, long long* __restrict__ gate, float* __restrict__ score) {
+           long long n_eff, long long row0, long long* __restrict__ gate, float* __restrict__ score,
+           const float* __restrict__ in_mu, const float* __restrict__ in_is) {
   constexpr int KQ = KP + KP * KP;
   const int lane = threadIdx.x;
   const int a = lane < KP ? lane : KP - 1;
@@ -258,7 +259,7 @@ score_slow(const float* __restrict__ X, int64_t ld, int d, int k, SubLayout lay,
       double y = 0.0, z = 0.0;
       const float* x = X + r * ld;
       for (int f = 0; f < d; ++f) {
-        const double xv = (double)x[f];
+        const double xv = (double)(in_mu ? __fmul_rn(__fsub_rn(x[f], in_mu[f]), in_is[f]) : x[f]);  // input transform
         double xc = xv;
         if (CLIP) xc = fmin(fmax(xv, lo[f]), hi[f]);
         const double v = V[(size_t)f * KP + a];
@@ -894,7 +895,7 @@ constexpr int kProjEvCap = 512;   // clipped elements listed per 16-row block; d
 
 // shared-memory carve-up of project_rows<NB>: sizes in bytes
 __host__ __device__ constexpr size_t proj_smem_bytes(int NB, bool clip) {
-  return (size_t)3 * 64 * NB * 4                      // mean, lo, hi
+  return (size_t)5 * 64 * NB * 4                      // mean, lo, hi, input transform (mu, 1/sigma)
          + (clip ? (size_t)64 * NB * 16 * 4 : 16)     // fp32 eigenvectors (sparse clip correction)
          + (size_t)NB * 16 * 32 * 16                  // B fragments
          + (clip ? (size_t)4 * kProjEvCap * 8 : 16)   // event lists, one per warp
@@ -907,10 +908,12 @@ __host__ __device__ constexpr size_t proj_smem_bytes(int NB, bool clip) {
 // A warp owns whole sub-segments, so it can also sum z and z z^T over each of them (Z^T Z on the tensor cores, same
 // 3xTF32 split): these are the projected sub-segment statistics that the prefix scan needs, i.e. V^T s and V^T G V of
 // the sub-segment without ever projecting a d x d partial.
-template <int NB, bool CLIP>
+// STD: rows are standardised on load, (x - in_mu) * in_is with the roundings of the stand-alone kernel (see pass 1).
+template <int NB, bool CLIP, bool STD>
 __global__ void __launch_bounds__(128, NB == 1 ? 4 : 3)
 project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float* __restrict__ mean_f,
-             const float* __restrict__ lo_f, const float* __restrict__ hi_f, const float* __restrict__ Vf,
+             const float* __restrict__ lo_f, const float* __restrict__ hi_f, const float* __restrict__ in_mu,
+             const float* __restrict__ in_is, const float* __restrict__ Vf,
              float* __restrict__ Zout, float* __restrict__ Dout, uint8_t* __restrict__ cflag,
              double* __restrict__ subproj) {
   constexpr int KP = 16, D = 64 * NB;
@@ -918,7 +921,9 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
   float* ms = reinterpret_cast<float*>(proj_smem);
   float* los = ms + D;
   float* his = los + D;
-  float* Vs = his + D;
+  float* smu = his + D;
+  float* sis = smu + D;
+  float* Vs = sis + D;
   uint4* vfrag = reinterpret_cast<uint4*>(Vs + (CLIP ? D * KP : 4));
   float2* evbase = reinterpret_cast<float2*>(vfrag + NB * 16 * 32);
   float* dtbase = reinterpret_cast<float*>(evbase + (CLIP ? 4 * kProjEvCap : 2));
@@ -933,6 +938,8 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
     ms[f] = mean_f[f];
     los[f] = CLIP ? lo_f[f] : 0.f;
     his[f] = CLIP ? hi_f[f] : 0.f;
+    smu[f] = STD ? in_mu[f] : 0.f;
+    sis[f] = STD ? in_is[f] : 0.f;
   }
   if (CLIP)
     for (int idx = threadIdx.x; idx < D * KP; idx += blockDim.x) Vs[idx] = Vf[idx];
@@ -997,6 +1004,16 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
         const int cbase = 64 * cc + 16 * q + 4 * t;
         const float4 m4 = *reinterpret_cast<const float4*>(ms + cbase);
         const float mm[4] = {m4.x, m4.y, m4.z, m4.w};
+        if (STD) {
+          const float4 u4 = *reinterpret_cast<const float4*>(smu + cbase);
+          const float4 s4 = *reinterpret_cast<const float4*>(sis + cbase);
+          const float uu[4] = {u4.x, u4.y, u4.z, u4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            ra[q][e] = __fmul_rn(__fsub_rn(ra[q][e], uu[e]), ss[e]);
+            rbv[q][e] = __fmul_rn(__fsub_rn(rbv[q][e], uu[e]), ss[e]);
+          }
+        }
         if (CLIP) {
           const float4 l4 = *reinterpret_cast<const float4*>(los + cbase);
           const float4 h4 = *reinterpret_cast<const float4*>(his + cbase);
@@ -1108,7 +1125,8 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
             const float* xr = X + (rb + row) * ld;
             float acc = 0.f;
             for (int f = 0; f < D; ++f) {
-              const float x = __ldg(xr + f);
+              float x = __ldg(xr + f);
+              if (STD) x = __fmul_rn(__fsub_rn(x, smu[f]), sis[f]);
               acc = fmaf(x - fminf(fmaxf(x, los[f]), his[f]), Vs[f * KP + jj], acc);
             }
             dt[row * KP + jj] = acc;
@@ -1535,18 +1553,25 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
     int pgrid = (int)ceil_div(nsub, 4);
     const int pmax = kNumSMs * (NBv == 1 ? 4 : 3);
     if (pgrid > pmax) pgrid = pmax;
-#define SB_LAUNCH_PROJECT(NB, CLIPV)                                                                               \
+#define SB_LAUNCH_PROJECT2(NB, CLIPV, STDV)                                                                         \
     do {                                                                                                           \
       const size_t psm = proj_smem_bytes(NB, CLIPV);                                                               \
-      SB_CUDA(cudaFuncSetAttribute(project_rows<NB, CLIPV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psm)); \
-      project_rows<NB, CLIPV><<<pgrid, 128, psm, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf,       \
-                                                      ws.proj_Z, ws.proj_D, ws.proj_flag, ws.subproj);             \
+      SB_CUDA(cudaFuncSetAttribute(project_rows<NB, CLIPV, STDV>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
+                                   (int)psm));                                                                     \
+      project_rows<NB, CLIPV, STDV><<<pgrid, 128, psm, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f,          \
+                                                            h->d_in_mu, h->d_in_is, h->d_Vf, ws.proj_Z, ws.proj_D, \
+                                                            ws.proj_flag, ws.subproj);                             \
+    } while (0)
+#define SB_LAUNCH_PROJECT(NB, CLIPV)                                                                               \
+    do {                                                                                                           \
+      if (h->d_in_mu) SB_LAUNCH_PROJECT2(NB, CLIPV, true); else SB_LAUNCH_PROJECT2(NB, CLIPV, false);              \
     } while (0)
     if (h->use_clip) {
       if (NBv == 1) SB_LAUNCH_PROJECT(1, true); else if (NBv == 2) SB_LAUNCH_PROJECT(2, true); else SB_LAUNCH_PROJECT(4, true);
     } else {
       if (NBv == 1) SB_LAUNCH_PROJECT(1, false); else if (NBv == 2) SB_LAUNCH_PROJECT(2, false); else SB_LAUNCH_PROJECT(4, false);
     }
+#undef SB_LAUNCH_PROJECT2
 #undef SB_LAUNCH_PROJECT
     SB_LAUNCH_CHECK();
     if (h->profile) cudaEventRecord(h->ev[7], st);
@@ -1570,11 +1595,11 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
     if (h->use_clip)
       score_slow<KP, true><<<grid, 32, 0, st>>>(X, ld, d, h->k, L, h->d_mean, h->d_lo, h->d_hi, h->d_V, h->d_PC0,
                                                ws.subproj, ws.sub_flags, (long long)h->n_eff, (long long)h->row0,
-                                               h->d_gate, score);
+                                               h->d_gate, score, h->d_in_mu, h->d_in_is);
     else
       score_slow<KP, false><<<grid, 32, 0, st>>>(X, ld, d, h->k, L, h->d_mean, h->d_lo, h->d_hi, h->d_V, h->d_PC0,
                                                 ws.subproj, ws.sub_flags, (long long)h->n_eff, (long long)h->row0,
-                                                h->d_gate, score);
+                                                h->d_gate, score, h->d_in_mu, h->d_in_is);
     SB_LAUNCH_CHECK();
     int g2 = (int)ceil_div(nsub, 4);
     if (g2 > kNumSMs * 4) g2 = kNumSMs * 4;

@@ -112,6 +112,27 @@ class OutlierMahalanobisB200(object):
         if self._h is not None:
             _cabi.check(_cabi.lib().sb_maha_set_option(self._h, option, value))
 
+    def fuse_standardise(self, transformer):
+        """Score every batch as if `transformer` (a StandardiseB200, or None to switch off) had been applied to it
+        first, without the separate pass over the batch: the graph `standardise -> outlier detector` of SURVEY 8
+        config 5 in one component.  Results equal those of the two components in sequence (same arithmetic per value;
+        scores within the detector's run-to-run spread of a few 1e-7, equal flags); only the
+        tensor-core shapes support it (d = 64, 128, 256 and n_components <= 16)."""
+        with self._lock:
+            self._fused = transformer
+            if self._h is not None:
+                self._apply_fused()
+
+    def _apply_fused(self):
+        t = getattr(self, "_fused", None)
+        if t is None:
+            _cabi.check(_cabi.lib().sb_maha_set_input_transform(self._h, None, None))
+            self._fused_params = None
+        else:
+            mu, inv = t._params(self._pick_device())
+            self._fused_params = (mu, inv)  # keep the device vectors alive while the handle points at them
+            _cabi.check(_cabi.lib().sb_maha_set_input_transform(self._h, mu.data_ptr(), inv.data_ptr()))
+
     def score_device(self, X):
         """One request batch resident on the GPU: X is a CUDA float32 tensor (rows, d), row-major.
 
@@ -230,6 +251,8 @@ class OutlierMahalanobisB200(object):
         self._h, self._d = h, d
         for opt, val in self._options.items():
             _cabi.check(L.sb_maha_set_option(self._h, opt, val))
+        if getattr(self, "_fused", None) is not None:
+            self._apply_fused()
         self._cached_state = None
         if self._restore is not None:
             self._push_state(self._restore)
@@ -306,12 +329,15 @@ class OutlierMahalanobisB200(object):
             out["_saved"] = st
             out["_saved_d"] = self._d
             out["_saved_options"] = dict(self._options)
+            t = getattr(self, "_fused", None)
+            out["_saved_fused"] = None if t is None else (t.mu, t.sigma)
             return out
 
     def __setstate__(self, state):
         saved = state.pop("_saved")
         d = state.pop("_saved_d")
         opts = state.pop("_saved_options", {})
+        fused = state.pop("_saved_fused", None)
         self.__dict__.update(state)
         self._device = None
         self._h = None
@@ -323,6 +349,11 @@ class OutlierMahalanobisB200(object):
         self._options = opts
         self._restore = saved if d is not None else None
         self._restore_d = d
+        self._fused = None
+        if fused is not None:
+            from .transformer import StandardiseB200
+
+            self._fused = StandardiseB200(fused[0], fused[1])
 
     def __del__(self):
         try:

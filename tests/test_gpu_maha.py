@@ -15,6 +15,7 @@ pytestmark = pytest.mark.gpu
 
 from oracle.mahalanobis import MahalanobisLean
 from seldon_core_b200 import OutlierMahalanobisB200, _cabi, synth
+from seldon_core_b200.errors import SeldonB200Error
 
 from conftest import GOLDEN
 from gpu_util import norm_err, projector_err, rel_err
@@ -225,3 +226,39 @@ def test_full_size_properties_c2():
     _, nf, ss = det._last_sums()
     assert nf == nflag and abs(ss - ssum) <= 1e-9 * abs(ssum)
     assert torch.isfinite(s1).all() and float(s1.min()) >= 0.0
+
+
+@pytest.mark.parametrize("d", [64, 256])
+def test_fused_standardise_equals_the_two_step_graph(d):
+    """standardise -> detector (SURVEY config 5) with the transformer fused into the detector's loads: the same
+    arithmetic per value, so scores agree with the two-component graph to the detector's own run-to-run spread (a few
+    1e-7 relative: the order of its shared-memory atomics) and flags are equal; shapes without the tensor-core path
+    refuse the fusion."""
+    import pickle
+
+    import torch
+
+    from seldon_core_b200 import StandardiseB200
+
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(5)
+    mu = torch.randn(d, generator=g, device=dev).double().cpu().numpy()
+    sigma = (0.5 + torch.rand(d, generator=g, device=dev)).double().cpu().numpy()
+    std = StandardiseB200(mu, sigma)
+    two, one = OutlierMahalanobisB200(n_components=16), OutlierMahalanobisB200(n_components=16)
+    one.fuse_standardise(std)
+    for i, rows in enumerate((40000, 70001, 128, 300000)):  # cold start (fp64 warm-up path), ragged, tiny, steady
+        Xs, _ = synth.maha_rows_torch(rows, d, 16, 400 + i, dev)
+        Xraw = (Xs * (torch.tensor(sigma, dtype=torch.float32, device=dev) + 1e-10)
+                + torch.tensor(mu, dtype=torch.float32, device=dev)).contiguous()
+        s2, f2 = two.score_device(std.transform_device(Xraw))
+        s1, f1 = one.score_device(Xraw)
+        assert float(((s1 - s2).abs() / s2.abs().clamp_min(1e-3)).max()) <= 2e-6 and torch.equal(f1, f2), i
+        if i == 1:
+            one = pickle.loads(pickle.dumps(one))
+    assert np.allclose(one.mean, two.mean, rtol=1e-6, atol=1e-9) and one.n == two.n
+    assert norm_err(one.C, two.C) <= 1e-6
+    odd = OutlierMahalanobisB200(n_components=3)
+    odd.fuse_standardise(StandardiseB200(mu[:18], sigma[:18]))
+    with pytest.raises(SeldonB200Error):
+        odd.score_device(torch.randn(500, 18, device=dev))
