@@ -98,6 +98,7 @@ struct sb_maha {
   double *d_V, *d_PC0;                     // [d][KP], [KP][KP]
   double* d_Vfull;                         // [d][d] full Jacobi basis of the previous batch (warm start)
   int warm_batches;                        // batches since the last cold start of the eigensolver
+  int no_cluster16;                        // a 16-CTA cluster launch failed once on this device: use 8
   const float *d_in_mu, *d_in_is;          // optional input transform (x - mu) * inv_sigma, caller-owned (sb_maha_set_input_transform)
   float* d_Vf;
   double* d_evals;                 // [KP]

@@ -9,9 +9,11 @@
 // orthogonal is applied to both.  At convergence W = C V has orthogonal columns, i.e. V diagonalises C^2 and
 // hence C, with |lambda_j| = ||W_j||.  Per step the d/2 disjoint pairs of a round-robin tournament are rotated
 // in parallel, one warp per pair, dot products by warp shuffles.  For 2*d*d*8 B <= 200 KB both matrices live
-// in shared memory (d <= 111), otherwise in the (L2-resident) workspace.  This is a latency kernel
+// in shared memory (d <= 111), otherwise in the (L2-resident) workspace.  d = 64 (jacobi64_regs) and d = 128 / 256
+// (jacobi_cluster) keep the columns in registers instead and exchange them between neighbouring pairs.  This is a latency kernel
 // (about 4*d^3 flops per sweep), not a roofline kernel; bench.py reports its time.
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "maha.cuh"
 
@@ -433,6 +435,175 @@ jacobi_topk_grid(const double* __restrict__ C, int d, int k, int KP, double* __r
   for (int idx = tid; idx < d * d; idx += nthr) Vfull[idx] = __ldcg(V + idx);
 }
 
+// d = 128 and 256: the register-resident odd-even scheme of jacobi64_regs spread over a cluster of eight CTAs.
+// One warp per column pair ("seat"; d/2 seats, d/16 per CTA), lane l holds rows (d/32) l .. of W and V of both columns.
+// Between two steps every seat keeps one column and passes the other to the neighbouring seat: the writer stores it
+// straight into the READER's shared memory - its own CTA's, or the neighbouring CTA's through distributed shared
+// memory - and one cluster barrier per step (hardware, a few hundred ns) replaces the cooperative grid barrier and the
+// L2 round trips of jacobi_topk_grid (about 4 us per step).  W = C V, the ranking and the outputs go through the
+// workspace copies of W and V as before.
+// NC CTAs per cluster (8 is the portable maximum, 16 needs the non-portable opt-in): the step is bound by the fp64 pipe
+// and the shared-memory traffic of each SM, so more SMs per problem shorten it.
+template <int D, int NC>
+__global__ void __launch_bounds__(D * 16 / NC, 1)
+jacobi_cluster(const double* __restrict__ C, int k, int KP, double* __restrict__ gW, double* __restrict__ gV,
+               double* __restrict__ Vd, float* __restrict__ Vf, double* __restrict__ evals,
+               long long* __restrict__ gate, double* __restrict__ Vfull, int warm, int* __restrict__ rot_flags) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  constexpr int SEATS = D / 2, SPC = SEATS / NC, PER = D / 32, CS = 2 * D;  // slot: W rows, then V rows
+  extern __shared__ double sm[];
+  double* bufE = sm;                    // [SPC + 1][CS]: slot s is read by local seat s; slot SPC parks position 0
+  double* bufO = sm + (SPC + 1) * CS;   // [SPC][CS]
+  __shared__ double norms[D];
+  const int cta = (int)cluster.block_rank();
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int seat = cta * SPC + warp;
+  const int gtid = cta * blockDim.x + tid, nthr = NC * blockDim.x;
+
+  for (int idx = gtid; idx < D * D; idx += nthr) {
+    const int c = idx / D, r = idx - c * D;
+    gV[idx] = warm ? Vfull[idx] : (r == c ? 1.0 : 0.0);
+  }
+  if (gtid < 64) rot_flags[gtid] = 0;
+  __threadfence();
+  cluster.sync();
+  for (int idx = gtid; idx < D * D; idx += nthr) {
+    const int c = idx / D, r = idx - c * D;
+    double acc;
+    if (warm) {
+      const double* vcol = gV + (size_t)c * D;
+      acc = 0.0;
+      for (int g = 0; g < D; ++g) acc = fma(C[(size_t)g * D + r], __ldcg(vcol + g), acc);  // C symmetric: coalesced
+    } else {
+      acc = C[idx];
+    }
+    gW[idx] = acc;
+  }
+  __threadfence();
+  cluster.sync();
+
+  double Xw[PER], Xv[PER], Yw[PER], Yv[PER];
+  auto load_col = [&](const double* w, const double* v, double (&cw)[PER], double (&cv)[PER]) {
+#pragma unroll
+    for (int i = 0; i < PER; i += 2) {
+      const double2 a = *reinterpret_cast<const double2*>(w + PER * lane + i);
+      const double2 b = *reinterpret_cast<const double2*>(v + PER * lane + i);
+      cw[i] = a.x; cw[i + 1] = a.y;
+      cv[i] = b.x; cv[i + 1] = b.y;
+    }
+  };
+  auto store_col = [&](double* w, double* v, const double (&cw)[PER], const double (&cv)[PER]) {
+#pragma unroll
+    for (int i = 0; i < PER; i += 2) {
+      *reinterpret_cast<double2*>(w + PER * lane + i) = make_double2(cw[i], cw[i + 1]);
+      *reinterpret_cast<double2*>(v + PER * lane + i) = make_double2(cv[i], cv[i + 1]);
+    }
+  };
+  load_col(gW + (size_t)(2 * seat) * D, gV + (size_t)(2 * seat) * D, Xw, Xv);
+  load_col(gW + (size_t)(2 * seat + 1) * D, gV + (size_t)(2 * seat + 1) * D, Yw, Yv);
+  // where this seat's outgoing columns go: the slot of the seat that reads them, in that seat's CTA
+  double* outE = seat == 0 ? bufE + SPC * CS
+                           : cluster.map_shared_rank(bufE, (seat - 1) / SPC) + ((seat - 1) % SPC) * CS;
+  double* outO = seat == SEATS - 1 ? nullptr
+                                   : cluster.map_shared_rank(bufO, (seat + 1) / SPC) + ((seat + 1) % SPC) * CS;
+  const double* inE = bufE + warp * CS;
+  const double* inO = seat == 0 ? bufE + SPC * CS : bufO + warp * CS;
+  cluster.sync();  // every CTA of the cluster is running before remote shared memory is touched
+
+  auto rotate = [&](bool active) {
+    double al = 0.0, be = 0.0, ga = 0.0;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+      al = fma(Xw[i], Xw[i], al);
+      be = fma(Yw[i], Yw[i], be);
+      ga = fma(Xw[i], Yw[i], ga);
+    }
+    al = warp_sum(al); be = warp_sum(be); ga = warp_sum(ga);
+    if (!active || al == 0.0 || be == 0.0) return false;
+    if (ga * ga <= 1e-22 * (al * be)) return false;  // |cos| <= 1e-11: orthogonal to working accuracy
+    const bool big = ga * ga > kQuadCos2 * (al * be);
+    const float zeta = __fdividef((float)(be - al), (float)(2.0 * ga));
+    const float tf = __fdividef(copysignf(1.f, zeta), fabsf(zeta) + sqrtf(fmaf(zeta, zeta, 1.f)));
+    if (!(fabsf(tf) > 0.f)) return false;
+    const double tt = (double)tf;
+    const double hh = fma(tt, tt, 1.0);
+    double cs = (double)rsqrtf((float)hh);  // fp32 seed, two Newton steps -> full fp64 accuracy
+    cs = cs * fma(-0.5 * hh, cs * cs, 1.5);
+    cs = cs * fma(-0.5 * hh, cs * cs, 1.5);
+    const double sn = cs * tt;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+      double a = Xw[i], b = Yw[i];
+      Xw[i] = cs * a - sn * b;
+      Yw[i] = sn * a + cs * b;
+      a = Xv[i]; b = Yv[i];
+      Xv[i] = cs * a - sn * b;
+      Yv[i] = sn * a + cs * b;
+    }
+    return big;
+  };
+
+  int sweeps = 0;
+  for (; sweeps < 40; ++sweeps) {
+    bool any = false;
+    for (int t = 0; t < D; t += 2) {
+      // even step: positions (2h, 2h+1) = (X, Y); afterwards Y moves down to the pair (2h-1, 2h) of seat h-1
+      any |= rotate(true);
+      store_col(outE, outE + D, Yw, Yv);
+      cluster.sync();
+      if (seat < SEATS - 1) load_col(inE, inE + D, Yw, Yv);
+      // odd step: positions (2h+1, 2h+2) = (X, Y) for h < SEATS-1; the last seat only keeps its X
+      any |= rotate(seat < SEATS - 1);
+      if (seat < SEATS - 1) store_col(outO, outO + D, Xw, Xv);
+      cluster.sync();
+      if (seat == SEATS - 1) {
+#pragma unroll
+        for (int i = 0; i < PER; ++i) { Yw[i] = Xw[i]; Yv[i] = Xv[i]; }
+      }
+      load_col(inO, inO + D, Xw, Xv);
+    }
+    if (any && lane == 0) rot_flags[sweeps] = 1;
+    __threadfence();
+    cluster.sync();
+    if (__ldcg(rot_flags + sweeps) == 0) break;
+  }
+  store_col(gW + (size_t)(2 * seat) * D, gV + (size_t)(2 * seat) * D, Xw, Xv);
+  store_col(gW + (size_t)(2 * seat + 1) * D, gV + (size_t)(2 * seat + 1) * D, Yw, Yv);
+  __threadfence();
+  cluster.sync();
+  // column norms, ranks and output by CTA 0 (small); the full basis for the next warm start by everyone
+  for (int idx = gtid; idx < D * D; idx += nthr) Vfull[idx] = __ldcg(gV + idx);
+  if (cta == 0) {
+    const int nw = blockDim.x >> 5;
+    for (int c = warp; c < D; c += nw) {
+      double acc = 0.0;
+      for (int r = lane; r < D; r += 32) { const double w = __ldcg(gW + (size_t)c * D + r); acc = fma(w, w, acc); }
+      acc = warp_sum(acc);
+      if (lane == 0) norms[c] = sqrt(acc);
+    }
+    __syncthreads();
+    for (int idx = tid; idx < D * KP; idx += blockDim.x) {
+      const int c = idx % KP;
+      if (c >= k) { Vd[idx] = 0.0; Vf[idx] = 0.f; }
+    }
+    for (int c = tid; c < D; c += blockDim.x) {
+      int rank = 0;
+      const double nc = norms[c];
+      for (int o = 0; o < D; ++o) rank += (norms[o] > nc) || (norms[o] == nc && o < c);
+      if (rank < k) {
+        evals[rank] = nc;
+        for (int f = 0; f < D; ++f) {
+          const double v = __ldcg(gV + (size_t)c * D + f);
+          Vd[(size_t)f * KP + rank] = v;
+          Vf[(size_t)f * KP + rank] = (float)v;
+        }
+      }
+    }
+    if (tid == 0) gate[3] = sweeps;
+  }
+}
+
 }  // namespace
 
 int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
@@ -445,6 +616,42 @@ int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
     const size_t sm64 = (size_t)(64 * 128 + 64 * 64) * sizeof(double);  // columns (W | V) + the staged covariance
     SB_CUDA(cudaFuncSetAttribute(jacobi64_regs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm64));
     jacobi64_regs<<<1, 512, sm64, st>>>(h->d_C1, h->k, h->KP, h->d_V, h->d_Vf, h->d_evals, h->d_gate, h->d_Vfull, warm);
+  } else if ((d == 128 || d == 256) && !h->force_generic) {
+    // cluster of 8 CTAs, columns in registers, neighbours exchange through (distributed) shared memory
+    int* flags = reinterpret_cast<int*>(h->d_gate + 8);
+    static const int nc = getenv("SB200_JACOBI_CLUSTER") ? atoi(getenv("SB200_JACOBI_CLUSTER")) : 16;
+    auto launch = [&](auto kernel, int ncta) -> cudaError_t {
+      const int spc = (d / 2) / ncta;
+      const size_t smc = (size_t)(2 * spc + 1) * 2 * d * sizeof(double);
+      cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc);
+      if (e == cudaSuccess && ncta > 8) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+      if (e != cudaSuccess) return e;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(ncta);
+      cfg.blockDim = dim3(spc * 32);
+      cfg.dynamicSmemBytes = smc;
+      cfg.stream = st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = ncta;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      return cudaLaunchKernelEx(&cfg, kernel, (const double*)h->d_C1, h->k, h->KP, ws.eig_W, ws.eig_V, h->d_V, h->d_Vf,
+                                h->d_evals, h->d_gate, h->d_Vfull, warm, flags);
+    };
+    // 16 CTAs per cluster where the device schedules it (a full GPU does), else the portable 8
+    cudaError_t ce = cudaErrorInvalidValue;
+    if (nc == 16 && !h->no_cluster16) {
+      ce = d == 128 ? launch(jacobi_cluster<128, 16>, 16) : launch(jacobi_cluster<256, 16>, 16);
+      if (ce != cudaSuccess) {
+        (void)cudaGetLastError();
+        h->no_cluster16 = 1;
+      }
+    }
+    if (ce != cudaSuccess) ce = d == 128 ? launch(jacobi_cluster<128, 8>, 8) : launch(jacobi_cluster<256, 8>, 8);
+    SB_CUDA(ce);
   } else if (need <= 200 * 1024) {
     SB_CUDA(cudaFuncSetAttribute(jacobi_topk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     jacobi_topk<true><<<1, 1024, need, st>>>(h->d_C1, d, h->k, h->KP, nullptr, nullptr, h->d_V, h->d_Vf, h->d_evals,
