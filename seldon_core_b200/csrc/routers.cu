@@ -640,9 +640,11 @@ router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon,
     }
   }
   __syncwarp();
-  if (lane == 0) s_cmd.exit = 1;
-  __syncwarp();
-  router_bar();  // helper warps leave
+  if (blockDim.x > 32) {  // Thompson launches carry helper warps: tell them to leave
+    if (lane == 0) s_cmd.exit = 1;
+    __syncwarp();
+    router_bar();
+  }
   const uint32_t* np_blk = s_np;
   if (windowed && win_built) {
     // commit the consumed part of the window: the state a draw-by-draw generator would be in
@@ -751,7 +753,7 @@ extern "C" int32_t sb_router_run(sb_router_t* h, int64_t T, const int64_t* d_row
   SB_REQUIRE(reward_mode != SB_REWARD_BERNOULLI || d_arm_p, SB_ERR_INVALID, "sb_router_run: arm probabilities required");
   SB_REQUIRE(!(h->kind == SB_ROUTER_EPSILON_GREEDY && h->n < 2), SB_ERR_INVALID,
              "epsilon-greedy needs >= 2 branches to explore (reference raises IndexError on random.choice([]))");
-  router_run_kernel<<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, (long long)T,
+  router_run_kernel<<<1, h->kind == SB_ROUTER_THOMPSON ? kRouterThreads : 32, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, (long long)T,
                                                        (const long long*)d_rows_per_call, d_reward, d_arm_p,
                                                        reward_mode, d_decisions, -1, 0.0, 0);
   SB_LAUNCH_CHECK();
@@ -762,7 +764,7 @@ extern "C" int32_t sb_router_feedback(sb_router_t* h, int32_t arm, int64_t rows,
   SB_REQUIRE(h && arm >= 0 && arm < h->n, SB_ERR_INVALID, "sb_router_feedback: routing %d outside 0..%d", arm,
              h ? h->n - 1 : 0);
   SB_REQUIRE(rows >= 1, SB_ERR_INVALID, "sb_router_feedback: rows must be >= 1 (reference divides by tries)");
-  router_run_kernel<<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, 1, nullptr, nullptr,
+  router_run_kernel<<<1, h->kind == SB_ROUTER_THOMPSON ? kRouterThreads : 32, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, 1, nullptr, nullptr,
                                                        nullptr, 0, nullptr, arm, reward, (long long)rows);
   SB_LAUNCH_CHECK();
   return SB_OK;
