@@ -1347,13 +1347,19 @@ chain4(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t
         t22 += __shfl_xor_sync(0xffffffffu, t22, o);
       }
       // g = w/(1 + w t) with w = (n+i)/(n+i+1)  ==  1/(1 + 1/(n+i) + t)
-      const float g1 = invr[r1] > 0.f ? __fdividef(1.f, 1.f + invr[r1] + t11) : 0.f;
+      // With d1 = 1 + 1/(n+i) + t11 and s2 = 1 + 1/(n+i+1) + t22:  g1 = 1/d1,  t2 = t22 - t12^2/d1,
+      // g2 = 1/(s2 - t12^2/d1) = d1/(d1 s2 - t12^2): the two reciprocals do not depend on each other.
+      const bool act1 = invr[r1] > 0.f, act2 = invr[r2] > 0.f;
+      const float d1 = 1.f + invr[r1] + t11, s2 = 1.f + invr[r2] + t22;
+      const float rd1 = __fdividef(1.f, d1);
+      const float rD = __fdividef(1.f, act1 ? fmaf(d1, s2, -t12 * t12) : s2);
+      const float g1 = act1 ? rd1 : 0.f;
+      const float g2 = act2 ? (act1 ? d1 * rD : rD) : 0.f;
       const float k12 = g1 * t12;
       float c2[4];
 #pragma unroll
       for (int q = 0; q < 4; ++q) c2[q] = fmaf(-k12, c1[q], d2[q]);
       const float t2 = fmaf(-k12, t12, t22);
-      const float g2 = invr[r2] > 0.f ? __fdividef(1.f, 1.f + invr[r2] + t2) : 0.f;
       float q1 = t11, q2 = t2;
       if (CLIP && blk_clip) {
         const bool f1 = __any_sync(0xffffffffu, ((cmask_cur >> r1) & 1u) != 0);
