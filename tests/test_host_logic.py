@@ -130,3 +130,25 @@ def test_gloo_two_rank_stats_exchange_matches_single_call():
     r0, r1 = sdist.shard_bounds(total_rows, world, 0)
     s0, G0 = MahalanobisLean(n_components=2)._stats(np.ascontiguousarray(X[r0:r1]), np.zeros(d))
     assert np.allclose(res[1][1], np.concatenate([[r1 - r0], s0, G0.ravel()]), rtol=1e-12, atol=1e-12)
+
+
+def test_json_ndarray_span_locates_the_value_without_parsing_numbers():
+    """Host side of the REST JSON decode: where the "ndarray" value starts and ends (utils.py:499-505 payload shape)."""
+    import json
+
+    import pytest
+
+    from seldon_core_b200 import codec
+    from seldon_core_b200.errors import SeldonB200Error
+
+    body = json.dumps({"meta": {"tags": {"a": "]]"}}, "data": {"ndarray": [[1, 2.5], [3, 4]], "names": ["x", "y"]}}).encode()
+    a, b, nd = codec.json_ndarray_span(body)
+    assert nd == 2 and json.loads(body[a:b]) == [[1, 2.5], [3, 4]]
+    body = b'{"data": {"names": ["t:0"], "ndarray" :\n [ [1.0 , 2.0] ,\n [3.0, 4.0]\n ] }}'
+    a, b, nd = codec.json_ndarray_span(body)
+    assert nd == 2 and json.loads(body[a:b]) == [[1.0, 2.0], [3.0, 4.0]]
+    a, b, nd = codec.json_ndarray_span(b'{"data":{"ndarray":[1,2,3]}}')
+    assert nd == 1 and a == 19 and b == 26
+    for bad in (b'{"data":{"tensor":{"shape":[1],"values":[1]}}}', b'{"data":{"ndarray":[[1,2],[3,4]'):
+        with pytest.raises(SeldonB200Error):
+            codec.json_ndarray_span(bad)
