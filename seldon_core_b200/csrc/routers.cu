@@ -408,12 +408,15 @@ __device__ __forceinline__ void win_beta(NpWindow& w, double a, double b, double
   *den = __dadd_rn(ga, gb);
 }
 
-// T calls.  kind 0 = epsilon-greedy, 1 = Thompson.  reward_mode -1: route only.
+// T calls.  KIND 0 = epsilon-greedy, 1 = Thompson (a template parameter so that the epsilon-greedy instance does not carry
+// the Thompson window code and its registers).  reward_mode -1: route only.
+template <int KIND>
 __global__ void __launch_bounds__(kRouterThreads)
-router_run_kernel(RouterState* __restrict__ st, int kind, int n, double epsilon, long long T,
+router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long T,
                   const long long* __restrict__ rows, const float* __restrict__ reward,
                   const float* __restrict__ arm_p, int reward_mode, int* __restrict__ decisions, int forced_arm,
                   double forced_reward, long long forced_rows) {
+  constexpr int kind = KIND;
   __shared__ uint32_t s_py[MT_N], s_np[MT_N], s_np2[MT_N];
   __shared__ double s_U[kWinD + 2], s_gret[kWinD], s_gcache[kWinD], s_E[kWinD];
   __shared__ uint8_t s_ok[kWinD];
@@ -753,9 +756,14 @@ extern "C" int32_t sb_router_run(sb_router_t* h, int64_t T, const int64_t* d_row
   SB_REQUIRE(reward_mode != SB_REWARD_BERNOULLI || d_arm_p, SB_ERR_INVALID, "sb_router_run: arm probabilities required");
   SB_REQUIRE(!(h->kind == SB_ROUTER_EPSILON_GREEDY && h->n < 2), SB_ERR_INVALID,
              "epsilon-greedy needs >= 2 branches to explore (reference raises IndexError on random.choice([]))");
-  router_run_kernel<<<1, h->kind == SB_ROUTER_THOMPSON ? kRouterThreads : 32, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, (long long)T,
-                                                       (const long long*)d_rows_per_call, d_reward, d_arm_p,
-                                                       reward_mode, d_decisions, -1, 0.0, 0);
+  if (h->kind == SB_ROUTER_THOMPSON)
+    router_run_kernel<1><<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, (long long)T,
+                                                                        (const long long*)d_rows_per_call, d_reward,
+                                                                        d_arm_p, reward_mode, d_decisions, -1, 0.0, 0);
+  else
+    router_run_kernel<0><<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, (long long)T,
+                                                            (const long long*)d_rows_per_call, d_reward, d_arm_p,
+                                                            reward_mode, d_decisions, -1, 0.0, 0);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }
@@ -764,8 +772,12 @@ extern "C" int32_t sb_router_feedback(sb_router_t* h, int32_t arm, int64_t rows,
   SB_REQUIRE(h && arm >= 0 && arm < h->n, SB_ERR_INVALID, "sb_router_feedback: routing %d outside 0..%d", arm,
              h ? h->n - 1 : 0);
   SB_REQUIRE(rows >= 1, SB_ERR_INVALID, "sb_router_feedback: rows must be >= 1 (reference divides by tries)");
-  router_run_kernel<<<1, h->kind == SB_ROUTER_THOMPSON ? kRouterThreads : 32, 0, (cudaStream_t)stream>>>(h->d_state, h->kind, h->n, h->epsilon, 1, nullptr, nullptr,
-                                                       nullptr, 0, nullptr, arm, reward, (long long)rows);
+  if (h->kind == SB_ROUTER_THOMPSON)
+    router_run_kernel<1><<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, 1, nullptr, nullptr,
+                                                                        nullptr, 0, nullptr, arm, reward, (long long)rows);
+  else
+    router_run_kernel<0><<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, 1, nullptr, nullptr, nullptr, 0,
+                                                            nullptr, arm, reward, (long long)rows);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }
