@@ -891,14 +891,16 @@ score_chain64(const float* __restrict__ X, int64_t ld, SubLayout lay, const floa
 //               for the rows that have a clipped feature (64 B for ~17 % of the rows);
 //   chain16   : lean registers, 16+ warps per SM, reads z back (L2/HBM) and walks the inverse chains.
 // Cost: ~150 B/row of extra DRAM traffic on top of the algorithmic 4*d + 8.
-constexpr int kProjEvCap = 512;   // clipped elements listed per 16-row block; denser blocks take the slow path
+// clipped elements listed per 16-row block; denser blocks take the slow path.  The wide shapes keep the list short so
+// that three CTAs fit in shared memory (78 KB -> 66 KB per CTA at d = 256; the expected count there is 11 per block)
+__host__ __device__ constexpr int proj_ev_cap(int NB) { return NB == 1 ? 512 : 128; }
 
 // shared-memory carve-up of project_rows<NB>: sizes in bytes
 __host__ __device__ constexpr size_t proj_smem_bytes(int NB, bool clip) {
   return (size_t)5 * 64 * NB * 4                      // mean, lo, hi, input transform (mu, 1/sigma)
          + (clip ? (size_t)64 * NB * 16 * 4 : 16)     // fp32 eigenvectors (sparse clip correction)
          + (size_t)NB * 16 * 32 * 16                  // B fragments
-         + (clip ? (size_t)4 * kProjEvCap * 8 : 16)   // event lists, one per warp
+         + (clip ? (size_t)4 * proj_ev_cap(NB) * 8 : 16)   // event lists, one per warp
          + (clip ? (size_t)4 * 16 * 16 * 4 : 16)      // y - z tiles, one per warp
          + 64                                         // event counters
          + (size_t)4 * 16 * 17 * 4;                   // z tiles for the Z^T Z fragments
@@ -926,12 +928,12 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
   float* Vs = sis + D;
   uint4* vfrag = reinterpret_cast<uint4*>(Vs + (CLIP ? D * KP : 4));
   float2* evbase = reinterpret_cast<float2*>(vfrag + NB * 16 * 32);
-  float* dtbase = reinterpret_cast<float*>(evbase + (CLIP ? 4 * kProjEvCap : 2));
+  float* dtbase = reinterpret_cast<float*>(evbase + (CLIP ? 4 * proj_ev_cap(NB) : 2));
   int* evcnt = reinterpret_cast<int*>(dtbase + (CLIP ? 4 * 16 * KP : 4));
   float* ztbase = reinterpret_cast<float*>(evcnt + 16);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
-  float2* evlist = evbase + (CLIP ? warp * kProjEvCap : 0);
+  float2* evlist = evbase + (CLIP ? warp * proj_ev_cap(NB) : 0);
   float* dt = dtbase + (CLIP ? warp * 16 * KP : 0);
   float* zt = ztbase + warp * 16 * 17;  // this block's z, [row][comp] padded to 17
   for (int f = threadIdx.x; f < D; f += blockDim.x) {
@@ -1036,7 +1038,7 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
                 const float xc = rr == 0 ? ca[e] : cb[e];
                 if (xc != x && (rr == 0 ? va : vb8)) {
                   const int slot = atomicAdd(&evcnt[warp], 1);
-                  if (slot < kProjEvCap)
+                  if (slot < proj_ev_cap(NB))
                     evlist[slot] = make_float2(__int_as_float((rr == 0 ? g : g + 8) * D + cbase + e), x - xc);
                 }
               }
@@ -1107,7 +1109,7 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
         __syncwarp();
         // y - z = V^T(x - clip(x)); lane (half, j) owns component j of rows 8 half .. 8 half + 7: no atomics
         const int half = lane >> 4, jj = lane & 15;
-        if (nev <= kProjEvCap) {
+        if (nev <= proj_ev_cap(NB)) {
           for (int k = 0; k < nev; ++k) {
             const float2 ev = evlist[k];
             const int rc = __float_as_int(ev.x), row = rc / D, col = rc - row * D;
@@ -1118,7 +1120,7 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
             }
           }
         } else {
-          // more than kProjEvCap clipped elements in 16 rows (degenerate data): recompute the block densely
+          // more than proj_ev_cap(NB) clipped elements in 16 rows (degenerate data): recompute the block densely
           rowmask = 0xffffu;
           for (int row = half; row < 16; row += 2) {
             if (rb + row >= r1) break;
