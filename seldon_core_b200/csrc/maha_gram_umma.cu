@@ -21,14 +21,15 @@
 //     d = 256: two accumulators (rows 0-127 x 256 columns, rows 128-255 x columns 128-255: the block below the
 //              diagonal is mirrored on store), 384 of the 512 TMEM columns, six MMAs per 8 rows.
 //
-// d = 64 additionally stages the raw rows in shared memory: a loader warp issues one cp.async.bulk per 32 KB chunk
-// into a 3-slot ring (mbarrier complete_tx), the producers read their float4 from there; the tile ring has two slots.
+// d = 64 and d = 256 additionally stage the raw rows in shared memory: a loader warp issues one cp.async.bulk per
+// 32 KB chunk into a ring (3 slots at d = 64, 2 at d = 256; mbarrier complete_tx), the producers read their float4 from
+// there; the tile ring then has two slots.  (d = 128 was measured faster with register prefetch.)
 //
 // Bounds (B200, measured, 16Mi rows): d = 64: 1.01 ms = 4.2 TB/s, 65 % of the measured HBM copy rate.  Shared-memory
 // bandwidth is the limiter: per 32 KB chunk 32 KB bulk-copy writes + 32 KB raw reads + 64 KB tile writes + 96 KB
 // operand reads by the MMAs = 224 KB at 128 B/clk = 1750 clk against 1424 clk of HBM time (without the raw staging the
-// kernel moved 160 KB per chunk but stalled on HBM latency: 1.07 ms).  d = 128: 2.7 TB/s, tensor pipe and HBM about
-// level.  d = 256: 2.1 TB/s, tensor pipe (2*d*d*0.75*3 flop per row).
+// kernel moved 160 KB per chunk but stalled on HBM latency: 1.07 ms).  d = 128: 3.4 TB/s.  d = 256: 2.7 TB/s; the operand
+// reads of the six MMAs per 8 rows (240 KB per 32 KB chunk) make shared-memory bandwidth the limiter there as well.
 #include "maha.cuh"
 
 namespace sb {
@@ -91,15 +92,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 
 // d = 64 is HBM-latency bound: its rows are staged raw in shared memory by bulk copies (cp.async.bulk, a loader warp;
 // three 32 KB slots in flight per SM cost no registers) and the tile ring gives up one slot for that.
-__host__ __device__ constexpr bool umma_raw_staged(int D) { return D == 64; }
+__host__ __device__ constexpr bool umma_raw_staged(int D) { return D == 64 || D == 256; }  // measured: d = 128 is faster without
 __host__ __device__ constexpr int umma_tile_stages(int D) { return umma_raw_staged(D) ? 2 : 3; }
-constexpr int kRawStages = 3;
+constexpr int kRawStagesMax = 3;
+__host__ __device__ constexpr int umma_raw_stages(int D) { return D == 64 ? 3 : 2; }  // d = 256 has 5 KB of constants more
 // rows per chunk: 8192 / D, so every tile is 32 KB and every thread converts four float4 per chunk
 __host__ __device__ constexpr int umma_chunk_rows(int D) { return 8192 / D; }
 
 __host__ __device__ constexpr size_t umma_smem_bytes(int D, int terms) {
   return (size_t)umma_tile_stages(D) * (terms == 3 ? 2 : 1) * umma_chunk_rows(D) * D * 4 +
-         (umma_raw_staged(D) ? (size_t)kRawStages * umma_chunk_rows(D) * D * 4 : 0) +
+         (umma_raw_staged(D) ? (size_t)umma_raw_stages(D) * umma_chunk_rows(D) * D * 4 : 0) +
          (D > 128 ? (size_t)5 * D * 4 : 0) /* mean, clip bounds, input transform when they do not fit in registers */ +
          1024 /* alignment slack */;
 }
@@ -126,6 +128,7 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   // hidden behind the MMAs of a 900-row sub-segment.)
   constexpr bool STACK = D == 64 && TERMS == 3;
   constexpr bool RAW = umma_raw_staged(D);
+  constexpr int kRawStages = umma_raw_stages(D);
   constexpr int kUmmaStages = umma_tile_stages(D);
   constexpr int RAWBYTES = umma_chunk_rows(D) * D * 4;
   constexpr uint32_t SBO = (STACK ? 2 : 1) * NSLAB * 512;  // between 4-row groups
@@ -144,8 +147,8 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
   float* his = los + D;
   __shared__ uint64_t bar_full[kUmmaStages];   // 16 producer warps have filled the slot
   __shared__ uint64_t bar_empty[kUmmaStages];  // the MMAs reading the slot have completed (tcgen05.commit)
-  __shared__ uint64_t bar_rfull[kRawStages];   // the bulk copy of a raw chunk has landed
-  __shared__ uint64_t bar_rempty[kRawStages];  // 16 producer warps have converted the raw chunk
+  __shared__ uint64_t bar_rfull[kRawStagesMax];   // the bulk copy of a raw chunk has landed
+  __shared__ uint64_t bar_rempty[kRawStagesMax];  // 16 producer warps have converted the raw chunk
   __shared__ uint64_t bar_acc;                 // all MMAs of the sub-segment have completed
   __shared__ uint64_t bar_tfree;               // 16 producer warps have drained the accumulator
   __shared__ uint32_t tmem_base_s;
