@@ -72,6 +72,69 @@ unpack_tensor_kernel(const uint8_t* __restrict__ vals, int64_t rows, int64_t col
   }
 }
 
+// 16-byte aligned, contiguous case: four values per thread (32 wire bytes <-> one float4), two groups in flight;
+// the column of a group advances by a fixed step per grid stride (no division in the loop)
+template <bool STD>
+__global__ void __launch_bounds__(256)
+unpack_tensor_vec4(const uint4* __restrict__ vals, int64_t n_grp, int q, const float4* __restrict__ mu,
+                   const float4* __restrict__ inv_sigma, float4* __restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int c = STD ? (int)(i % q) : 0;
+  const int step = STD ? (int)(stride % q) : 0;
+  constexpr int U = 2;
+  for (; i < n_grp; i += U * stride) {
+    uint4 a[U], b[U];
+    int cc[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      cc[u] = c;
+      c += step;
+      if (c >= q) c -= q;
+      const int64_t k = i + u * stride;
+      if (k < n_grp) { a[u] = __ldcs(vals + 2 * k); b[u] = __ldcs(vals + 2 * k + 1); }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t k = i + u * stride;
+      if (k >= n_grp) break;
+      double v0 = __hiloint2double((int)a[u].y, (int)a[u].x), v1 = __hiloint2double((int)a[u].w, (int)a[u].z);
+      double v2 = __hiloint2double((int)b[u].y, (int)b[u].x), v3 = __hiloint2double((int)b[u].w, (int)b[u].z);
+      if (STD) {
+        const float4 m = __ldg(mu + cc[u]), s = __ldg(inv_sigma + cc[u]);
+        v0 = (v0 - (double)m.x) * (double)s.x; v1 = (v1 - (double)m.y) * (double)s.y;
+        v2 = (v2 - (double)m.z) * (double)s.z; v3 = (v3 - (double)m.w) * (double)s.w;
+      }
+      sb::stg_stream_f4(out + k, make_float4((float)v0, (float)v1, (float)v2, (float)v3));
+    }
+  }
+}
+
+// two values per thread: an 8-byte load and one 16-byte store, both contiguous across the warp; four pairs in flight
+template <typename TIn>
+__global__ void __launch_bounds__(256)
+pack_tensor_vec2(const uint2* __restrict__ in, int64_t n_pair, uint4* __restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  constexpr int U = 4;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pair; i += U * stride) {
+    uint2 x[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (i + u * stride < n_pair) x[u] = __ldcs(in + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t k = i + u * stride;
+      if (k >= n_pair) break;
+      TIn t0, t1;
+      memcpy(&t0, &x[u].x, 4);
+      memcpy(&t1, &x[u].y, 4);
+      const double d0 = (double)t0, d1 = (double)t1;
+      __stcs(out + k, make_uint4((uint32_t)__double2loint(d0), (uint32_t)__double2hiint(d0), (uint32_t)__double2loint(d1),
+                                 (uint32_t)__double2hiint(d1)));
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256)
 unpack_listvalue_kernel(const uint8_t* __restrict__ wire, int64_t rows, int64_t cols, int64_t row_bytes, int hdr,
                         uint64_t l1, uint64_t l2, float* __restrict__ out, int64_t ld, int32_t* __restrict__ status) {
@@ -607,6 +670,20 @@ extern "C" int32_t sb_unpack_tensor_f64(const uint8_t* d_wire, uint64_t values_o
   const int aligned = ((uintptr_t)vals & 7) == 0;
   const int grid = grid_for(rows * cols, 4);
   cudaStream_t st = (cudaStream_t)stream;
+  const int64_t total = rows * cols;
+  const bool vec = ld == cols && total % 4 == 0 && (((uintptr_t)vals | (uintptr_t)d_out) & 15) == 0 &&
+                   (!d_mu || (cols % 4 == 0 && (((uintptr_t)d_mu | (uintptr_t)d_inv_sigma) & 15) == 0));
+  if (vec) {
+    const int64_t n_grp = total / 4;
+    const int g4 = grid_for(n_grp, 2);
+    if (d_mu)
+      unpack_tensor_vec4<true><<<g4, 256, 0, st>>>((const uint4*)vals, n_grp, (int)(cols / 4), (const float4*)d_mu,
+                                                  (const float4*)d_inv_sigma, (float4*)d_out);
+    else
+      unpack_tensor_vec4<false><<<g4, 256, 0, st>>>((const uint4*)vals, n_grp, 1, nullptr, nullptr, (float4*)d_out);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+  }
   if (d_mu)
     unpack_tensor_kernel<true><<<grid, 256, 0, st>>>(vals, rows, cols, d_mu, d_inv_sigma, d_out, ld, aligned);
   else
@@ -668,6 +745,15 @@ extern "C" int32_t sb_pack_tensor_f64(const void* d_in, int32_t in_dtype, int64_
   SB_REQUIRE(d_in && d_wire_values, SB_ERR_INVALID, "sb_pack_tensor_f64: null buffer");
   const int aligned = ((uintptr_t)d_wire_values & 7) == 0;
   cudaStream_t st = (cudaStream_t)stream;
+  if (n % 2 == 0 && ((uintptr_t)d_in & 7) == 0 && ((uintptr_t)d_wire_values & 15) == 0) {
+    const int64_t n_pair = n / 2;
+    if (in_dtype == SB_F32)
+      pack_tensor_vec2<float><<<grid_for(n_pair, 4), 256, 0, st>>>((const uint2*)d_in, n_pair, (uint4*)d_wire_values);
+    else
+      pack_tensor_vec2<int32_t><<<grid_for(n_pair, 4), 256, 0, st>>>((const uint2*)d_in, n_pair, (uint4*)d_wire_values);
+    SB_LAUNCH_CHECK();
+    return SB_OK;
+  }
   if (in_dtype == SB_F32)
     pack_tensor_kernel<float><<<grid_for(n, 4), 256, 0, st>>>((const float*)d_in, n, d_wire_values, aligned);
   else
