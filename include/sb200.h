@@ -36,9 +36,10 @@ int32_t sb_version(void);
 /* ------------------------------------------------------------------------------------------------ codec
  * replaces python/seldon_core/utils.py:161-169 (grpc_datadef_to_array, tensor branch): the packed doubles of
  * a serialised Tensor start `values_off` bytes into `d_wire`; they are converted to fp32 rows of `d_out`
- * (leading dimension ld).  d_mu / d_inv_sigma (both or neither) fuse the standardise transformer
+ * (leading dimension ld); the wire holds wire_nbytes bytes and a shape that claims more values than it carries is
+ * rejected with SB_ERR_INVALID (the reference raises on the reshape, utils.py:169).  d_mu / d_inv_sigma (both or neither) fuse the standardise transformer
  * (components/outlier-detection/vae/CoreVAE.py:128): out = (x - mu) * inv_sigma, inv_sigma = 1/(sigma+1e-10). */
-int32_t sb_unpack_tensor_f64(const uint8_t* d_wire, uint64_t values_off, int64_t rows, int64_t cols,
+int32_t sb_unpack_tensor_f64(const uint8_t* d_wire, uint64_t wire_nbytes, uint64_t values_off, int64_t rows, int64_t cols,
                              const float* d_mu, const float* d_inv_sigma, float* d_out, int64_t ld,
                              uintptr_t stream);
 
@@ -212,12 +213,25 @@ int32_t sb_router_destroy(sb_router_t* h);
 /* d_rows_per_call may be NULL (1 row per call).  route only: reward_mode = -1 (no feedback applied). */
 int32_t sb_router_run(sb_router_t* h, int64_t T, const int64_t* d_rows_per_call, const float* d_reward,
                       const float* d_arm_p, int32_t reward_mode, int32_t* d_decisions, uintptr_t stream);
+/* route() of the class API (EpsilonGreedy.py:87-106, ThompsonSampling.py:78-91): one decision, written by the kernel
+ * into pinned host memory owned by the handle and returned in *h_out.  Synchronises the stream. */
+int32_t sb_router_route(sb_router_t* h, int32_t* h_out, uintptr_t stream);
+/* Thompson: the n beta samples of the last route (self.branch_values, ThompsonSampling.py:81-82).  Synchronises. */
+int32_t sb_router_last_values(sb_router_t* h, double* h_values, uintptr_t stream);
 /* single feedback for an externally chosen arm (send_feedback of the class API) */
 int32_t sb_router_feedback(sb_router_t* h, int32_t arm, int64_t rows, double reward, uintptr_t stream);
 /* state blob for pickling: success[n], tries[n], best_branch, then both generator states.  Synchronises. */
 int64_t sb_router_state_len(const sb_router_t* h);
 int32_t sb_router_get_state(sb_router_t* h, int64_t* h_state, uintptr_t stream);
 int32_t sb_router_set_state(sb_router_t* h, const int64_t* h_state, uintptr_t stream);
+/* out2 = { accept/reject comparisons of the legacy gamma sampler (ThompsonSampling.py:81 -> np.random.beta) that fell
+ * inside the libm guard band and were decided again with correctly rounded logarithms, beta draws taken draw by draw
+ * because they outran the kernel's look-ahead window } since the handle was created.  Synchronises. */
+int32_t sb_router_counters(sb_router_t* h, int64_t* out2, uintptr_t stream);
+/* test knob: SB_ROUTER_OPT_DEBUG_FALLBACK_PERIOD p > 0 takes every p-th beta draw through the draw-by-draw fallback
+ * (decisions must not change); 0 = off */
+#define SB_ROUTER_OPT_DEBUG_FALLBACK_PERIOD 1
+int32_t sb_router_set_option(sb_router_t* h, int32_t option, int64_t value);
 
 #ifdef __cplusplus
 }

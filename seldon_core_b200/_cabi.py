@@ -13,6 +13,7 @@ SB_F32, SB_I32 = 0, 1
 SB_OPT_GRAM_TERMS, SB_OPT_FORCE_GENERIC, SB_OPT_PROFILE, SB_OPT_FUSED_PASS2, SB_OPT_LEGACY_MMA = 1, 2, 3, 4, 5
 SB_ROUTER_EPSILON_GREEDY, SB_ROUTER_THOMPSON = 0, 1
 SB_REWARD_PER_CALL, SB_REWARD_TABLE, SB_REWARD_BERNOULLI = 0, 1, 2
+SB_ROUTER_OPT_DEBUG_FALLBACK_PERIOD = 1
 
 _uintptr = ctypes.c_size_t
 _pp = POINTER(c_void_p)
@@ -22,7 +23,7 @@ SIGNATURES = {
     "sb_last_error": (c_char_p, []),
     "sb_version": (c_int32, []),
     "sb_launch_count": (c_int64, []),
-    "sb_unpack_tensor_f64": (c_int32, [c_void_p, c_uint64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64, _uintptr]),
+    "sb_unpack_tensor_f64": (c_int32, [c_void_p, c_uint64, c_uint64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64, _uintptr]),
     "sb_unpack_listvalue": (c_int32, [c_void_p, c_uint64, c_int64, c_int64, c_void_p, c_int64, c_void_p, _uintptr]),
     "sb_pack_tensor_f64": (c_int32, [c_void_p, c_int32, c_int64, c_void_p, _uintptr]),
     "sb_pack_listvalue": (c_int32, [c_void_p, c_int32, c_int64, c_int64, c_void_p, _uintptr]),
@@ -63,6 +64,10 @@ SIGNATURES = {
     "sb_router_state_len": (c_int64, [c_void_p]),
     "sb_router_get_state": (c_int32, [c_void_p, c_void_p, _uintptr]),
     "sb_router_set_state": (c_int32, [c_void_p, c_void_p, _uintptr]),
+    "sb_router_route": (c_int32, [c_void_p, POINTER(c_int32), _uintptr]),
+    "sb_router_last_values": (c_int32, [c_void_p, c_void_p, _uintptr]),
+    "sb_router_counters": (c_int32, [c_void_p, c_void_p, _uintptr]),
+    "sb_router_set_option": (c_int32, [c_void_p, c_int32, c_int64]),
 }
 
 _lib = None

@@ -55,16 +55,36 @@ def _upload(wire, dev, offset_to_align):
 
 
 def parse_tensor_header(wire):
-    """Shape and offset of the packed doubles of a serialised Tensor (proto/prediction.proto:33-38)."""
-    pos, shape = 0, []
-    if wire[:1] == b"\x0a":
-        n, pos = _read_varint(wire, 1)
-        end = pos + n
-        while pos < end:
-            v, pos = _read_varint(wire, pos)
-            shape.append(v)
-    count = int(np.prod(shape)) if shape else 0
-    return shape, len(wire) - 8 * count  # utils.py:164-169: the values are the tail of the message
+    """Shape and offset of the packed doubles of a serialised Tensor (proto/prediction.proto:33-38):
+    `0a <len> <varint dims>` then `12 <len> <little-endian doubles>`, the values last (utils.py:164-169 reads the
+    tail).  A payload whose values field is absent, is not the tail, or does not hold prod(shape) doubles raises -
+    the reference fails on the reshape (utils.py:169)."""
+    pos, shape, n = 0, [], len(wire)
+    try:
+        if wire[:1] == b"\x0a":
+            ln, pos = _read_varint(wire, 1)
+            end = pos + ln
+            if end > n:
+                raise IndexError
+            while pos < end:
+                v, pos = _read_varint(wire, pos)
+                shape.append(v)
+        count = 1
+        for v in shape:
+            count *= int(v)
+        if not shape:
+            count = 0
+        if pos == n and count == 0:
+            return shape, n
+        if wire[pos:pos + 1] != b"\x12":
+            raise SeldonB200Error("tensor payload: no packed `values` field after the shape")
+        vlen, pos = _read_varint(wire, pos + 1)
+    except IndexError:
+        raise SeldonB200Error("tensor payload is truncated")
+    if vlen != 8 * count or pos + vlen != n:
+        raise SeldonB200Error("tensor payload: shape %s needs %d bytes of values, the message carries %d"
+                              % (shape, 8 * count, n - pos))
+    return shape, pos
 
 
 def decode_tensor(wire, device=None, mu=None, inv_sigma=None):
@@ -79,7 +99,7 @@ def decode_tensor(wire, device=None, mu=None, inv_sigma=None):
     buf, pad = _upload(wire, dev, off)
     out = torch.empty((rows, cols), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
-        _cabi.check(_cabi.lib().sb_unpack_tensor_f64(buf.data_ptr(), pad + off, rows, cols,
+        _cabi.check(_cabi.lib().sb_unpack_tensor_f64(buf.data_ptr(), buf.numel(), pad + off, rows, cols,
                                                      None if mu is None else mu.data_ptr(),
                                                      None if inv_sigma is None else inv_sigma.data_ptr(),
                                                      out.data_ptr(), cols, torch.cuda.current_stream().cuda_stream))

@@ -659,11 +659,16 @@ extern "C" uint64_t sb_tensor_values_offset(int64_t rows, int64_t cols) {
   return 1 + varint_len(shape_bytes) + shape_bytes + 1 + varint_len(8ull * (uint64_t)rows * (uint64_t)cols);
 }
 
-extern "C" int32_t sb_unpack_tensor_f64(const uint8_t* d_wire, uint64_t values_off, int64_t rows, int64_t cols,
+extern "C" int32_t sb_unpack_tensor_f64(const uint8_t* d_wire, uint64_t wire_nbytes, uint64_t values_off, int64_t rows,
+                                        int64_t cols,
                                         const float* d_mu, const float* d_inv_sigma, float* d_out, int64_t ld,
                                         uintptr_t stream) {
   SB_REQUIRE(rows >= 0 && cols >= 1 && ld >= cols, SB_ERR_INVALID, "sb_unpack_tensor_f64: bad shape");
   SB_REQUIRE((d_mu == nullptr) == (d_inv_sigma == nullptr), SB_ERR_INVALID, "sb_unpack_tensor_f64: mu and inv_sigma go together");
+  SB_REQUIRE(values_off <= wire_nbytes && (uint64_t)rows <= (wire_nbytes - values_off) / 8 / (uint64_t)cols, SB_ERR_INVALID,
+             "sb_unpack_tensor_f64: shape %lld x %lld needs %llu bytes of values at offset %llu, the payload has %llu",
+             (long long)rows, (long long)cols, (unsigned long long)(8ull * rows * cols), (unsigned long long)values_off,
+             (unsigned long long)wire_nbytes);
   if (rows == 0) return SB_OK;
   SB_REQUIRE(d_wire && d_out, SB_ERR_INVALID, "sb_unpack_tensor_f64: null buffer");
   const uint8_t* vals = d_wire + values_off;

@@ -183,13 +183,23 @@ extern "C" int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t valu
 
 extern "C" int32_t sb_maha_pass1_stats(sb_maha_t* h, const float* d_X, int64_t rows, int64_t ld, void* d_ws,
                                        uint64_t ws_bytes, double* d_stats_out, uintptr_t stream) {
-  SB_REQUIRE(h && d_X && rows >= 1 && ld >= h->d, SB_ERR_INVALID, "sb_maha_pass1_stats: bad arguments");
+  SB_REQUIRE(h && rows >= 0 && (rows == 0 || (d_X && ld >= h->d)), SB_ERR_INVALID, "sb_maha_pass1_stats: bad arguments");
   SB_REQUIRE(h->stage == 0, SB_ERR_STATE, "sb_maha_pass1_stats: previous batch not committed");
   MahaWs ws;
-  int rc = get_ws(h, rows, d_ws, ws_bytes, &ws);
+  int rc = get_ws(h, rows > 0 ? rows : 1, d_ws, ws_bytes, &ws);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   h->rows_local = rows;
+  if (rows == 0) {
+    // a rank that holds no row of this request batch (fewer rows than ranks): its record is all zeros; it still takes
+    // part in the exchange, forms the same covariance, eigenvectors and state, and scores nothing
+    SB_CUDA(cudaMemsetAsync(d_stats_out ? d_stats_out : ws.stats, 0, (size_t)sb_maha_stats_len(h) * sizeof(double), st));
+    h->n_eff = (h->max_n > 0 && h->n > h->max_n) ? h->max_n : h->n;
+    h->use_clip = (h->n > h->start_clip) && h->has_clip;
+    h->lay = h->lay2 = make_layout(1);
+    h->stage = 1;
+    return SB_OK;
+  }
   h->lay = make_layout(rows);
   h->n_eff = (h->max_n > 0 && h->n > h->max_n) ? h->max_n : h->n;  // CoreMahalanobis.py:79-82
   h->use_clip = (h->n > h->start_clip) && h->has_clip;               // L85 (uncapped n)
@@ -210,11 +220,13 @@ extern "C" int32_t sb_maha_finalize(sb_maha_t* h, const double* d_all_stats, int
                                     uintptr_t stream) {
   SB_REQUIRE(h && nranks >= 1 && rank >= 0 && rank < nranks, SB_ERR_INVALID, "sb_maha_finalize: bad arguments");
   SB_REQUIRE(h->stage == 1, SB_ERR_STATE, "sb_maha_finalize: call sb_maha_pass1_stats first");
+  SB_REQUIRE(total_rows >= 1 && (h->rows_local > 0 || (d_all_stats && nranks > 1)), SB_ERR_INVALID,
+             "sb_maha_finalize: an empty shard needs the records of the other ranks");
   SB_REQUIRE(total_rows >= h->rows_local && row0 >= 0 && row0 + h->rows_local <= total_rows, SB_ERR_INVALID,
              "sb_maha_finalize: shard [%lld, +%lld) outside a batch of %lld rows", (long long)row0,
              (long long)h->rows_local, (long long)total_rows);
   MahaWs ws;
-  int rc = get_ws(h, h->rows_local, d_ws, ws_bytes, &ws);
+  int rc = get_ws(h, h->rows_local > 0 ? h->rows_local : 1, d_ws, ws_bytes, &ws);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   h->rows_total = total_rows;
@@ -222,16 +234,22 @@ extern "C" int32_t sb_maha_finalize(sb_maha_t* h, const double* d_all_stats, int
   const double* all = d_all_stats ? d_all_stats : ws.stats;
   if ((rc = launch_finalize_cov(h, all, nranks, rank, ws, st))) return rc;
   if ((rc = launch_eigh(h, ws, st))) return rc;
-  if ((rc = launch_prefix(h, ws, ws.rank_proj, st))) return rc;
+  if (h->rows_local > 0 && (rc = launch_prefix(h, ws, ws.rank_proj, st))) return rc;
   h->stage = 2;
   return SB_OK;
 }
 
 extern "C" int32_t sb_maha_pass2_score(sb_maha_t* h, const float* d_X, int64_t rows, int64_t ld, float* d_score,
                                        int32_t* d_flag, void* d_ws, uint64_t ws_bytes, uintptr_t stream) {
-  SB_REQUIRE(h && d_X && d_score && d_flag && ld >= h->d, SB_ERR_INVALID, "sb_maha_pass2_score: bad arguments");
+  SB_REQUIRE(h && (rows == 0 || (d_X && d_score && d_flag && ld >= h->d)), SB_ERR_INVALID, "sb_maha_pass2_score: bad arguments");
   SB_REQUIRE(h->stage == 2, SB_ERR_STATE, "sb_maha_pass2_score: call sb_maha_finalize first");
   SB_REQUIRE(rows == h->rows_local, SB_ERR_INVALID, "sb_maha_pass2_score: rows differ from pass 1");
+  if (rows == 0) {  // empty shard: nothing to score; the sums of the last batch read as zero
+    SB_CUDA(cudaMemsetAsync(h->d_gate + 2, 0, sizeof(long long), (cudaStream_t)stream));
+    SB_CUDA(cudaMemsetAsync(h->d_score_sum, 0, sizeof(double), (cudaStream_t)stream));
+    h->stage = 3;
+    return SB_OK;
+  }
   SB_REQUIRE(!h->split_pass2 || ((ld % 4 == 0) && (((uintptr_t)d_X & 15) == 0)), SB_ERR_INVALID,
              "sb_maha_pass2_score: X must have the alignment it had in pass 1");
   MahaWs ws;

@@ -33,6 +33,9 @@ struct RouterState {
   long long succ[kMaxArms];
   long long tries[kMaxArms];
   int best;
+  long long guard_hits;  // accept/reject comparisons that fell inside the libm guard band (resolved with cr_log)
+  long long fallbacks;   // beta draws taken draw by draw because they outran the look-ahead window
+  double last_values[kMaxArms];  // Thompson: the beta samples of the last route (branch_values of the reference class)
 };
 
 __host__ __device__ inline void mt_init_genrand(MtState* g, uint32_t s) {
@@ -68,6 +71,8 @@ struct DevMt {
   int pos;
   int has_gauss;
   double gauss;
+  int guard;   // guard-band hits of the draws made through this generator
+  int regens;  // block regenerations since construction
 };
 
 __device__ __forceinline__ uint32_t mt_twist_word(uint32_t cur, uint32_t nxt, uint32_t far) {
@@ -109,6 +114,7 @@ __device__ __forceinline__ uint32_t mt_u32(DevMt& g) {
   if (g.pos >= MT_N) {  // warp-uniform
     mt_regenerate(g.mt);
     g.pos = 0;
+    ++g.regens;
   }
   uint32_t y = g.mt[g.pos++];
   y ^= y >> 11;
@@ -139,6 +145,90 @@ __device__ __forceinline__ uint32_t np_choice_index(DevMt& g, uint32_t m) {
     const uint32_t v = mt_u32(g) & mask;
     if (v <= rng) return v;
   }
+}
+
+// ---- libm guard band ------------------------------------------------------------------------------------------------
+// The legacy samplers decide accept/reject by comparing fp64 expressions that contain log().  glibc's log (what the
+// reference runs on) is correctly rounded in all but a vanishing fraction of arguments; CUDA's is within 1 ulp of that.
+// A comparison whose two sides are further apart than any such difference decides the same way on both; one that falls
+// inside the band below is decided again with logarithms computed in double-double arithmetic and rounded once
+// (cr_log), i.e. with the values glibc returns.  Everything else in the expressions is +, -, *, /, sqrt, which are
+// IEEE-exact on both sides.  (The Gaussian x entering the test carries its own log; a 1-ulp difference there moves both
+// sides by ~1e-16 relative, four thousand times less than the band, so it cannot change which side of the band a
+// comparison falls on - it can only matter inside a band hit, which the counters report.)
+struct dd { double hi, lo; };
+__device__ __forceinline__ dd dd_two_sum(double a, double b) {
+  const double s = __dadd_rn(a, b), bb = __dadd_rn(s, -a);
+  return dd{s, __dadd_rn(__dadd_rn(a, -__dadd_rn(s, -bb)), __dadd_rn(b, -bb))};
+}
+__device__ __forceinline__ dd dd_quick(double a, double b) {
+  const double s = __dadd_rn(a, b);
+  return dd{s, __dadd_rn(b, -__dadd_rn(s, -a))};
+}
+__device__ __forceinline__ dd dd_prod(double a, double b) {
+  const double p = __dmul_rn(a, b);
+  return dd{p, __fma_rn(a, b, -p)};
+}
+__device__ __forceinline__ dd dd_add(dd a, dd b) {
+  dd s = dd_two_sum(a.hi, b.hi);
+  const dd t = dd_two_sum(a.lo, b.lo);
+  s.lo = __dadd_rn(s.lo, t.hi);
+  s = dd_quick(s.hi, s.lo);
+  s.lo = __dadd_rn(s.lo, t.lo);
+  return dd_quick(s.hi, s.lo);
+}
+__device__ __forceinline__ dd dd_mul(dd a, dd b) {
+  dd p = dd_prod(a.hi, b.hi);
+  p.lo = __dadd_rn(p.lo, __dadd_rn(__dmul_rn(a.hi, b.lo), __dmul_rn(a.lo, b.hi)));
+  return dd_quick(p.hi, p.lo);
+}
+__device__ __forceinline__ dd dd_neg(dd a) { return dd{-a.hi, -a.lo}; }
+__device__ __forceinline__ dd dd_div(dd a, dd b) {
+  const double q1 = a.hi / b.hi;
+  dd r = dd_add(a, dd_neg(dd_mul(b, dd{q1, 0.0})));
+  const double q2 = r.hi / b.hi;
+  r = dd_add(r, dd_neg(dd_mul(b, dd{q2, 0.0})));
+  const double q3 = r.hi / b.hi;
+  return dd_add(dd_quick(q1, q2), dd{q3, 0.0});
+}
+// log(x), x > 0 finite, to ~2^-100 and rounded once to binary64: x = 2^e m with m in [sqrt(1/2), sqrt(2)),
+// log m = 2 atanh(s), s = (m - 1)/(m + 1), |s| <= 0.1716: 22 terms of the odd series in double-double
+__device__ __noinline__ double cr_log(double x) {
+  int e;
+  double m = frexp(x, &e);  // m in [0.5, 1)
+  if (m < 0.70710678118654752440) { m = __dmul_rn(m, 2.0); --e; }
+  const dd num = dd{__dadd_rn(m, -1.0), 0.0};  // exact (Sterbenz)
+  const dd den = dd_two_sum(m, 1.0);
+  const dd s = dd_div(num, den);
+  const dd s2 = dd_mul(s, s);
+  dd acc = dd_div(dd{1.0, 0.0}, dd{43.0, 0.0});
+  for (int k = 20; k >= 0; --k) acc = dd_add(dd_mul(acc, s2), dd_div(dd{1.0, 0.0}, dd{(double)(2 * k + 1), 0.0}));
+  dd r = dd_mul(s, acc);
+  r = dd{__dmul_rn(r.hi, 2.0), __dmul_rn(r.lo, 2.0)};
+  const dd ln2 = dd{0.69314718055994530942, 2.3190468138462995584e-17};
+  r = dd_add(dd_mul(ln2, dd{(double)e, 0.0}), r);
+  return __dadd_rn(r.hi, r.lo);
+}
+
+// second acceptance test of the Marsaglia-Tsang gamma loop: log(U) < 0.5*X*X + b*(1 - V + log(V)), evaluated without
+// fused multiply-add in the operation order of the C source of NumPy's legacy generator
+__device__ __forceinline__ bool mt_accept(double u, double x, double v, double b, int& guard) {
+  const double lu = log(u), lv = log(v);
+  const double hx = __dmul_rn(__dmul_rn(0.5, x), x), omv = __dadd_rn(1.0, -v);
+  const double rhs = __dadd_rn(hx, __dmul_rn(b, __dadd_rn(omv, lv)));
+  // the band scales with the terms that cancel inside rhs (b*(1-v) against b*log(v) for large shapes)
+  const double band = 0x1p-40 * (fabs(lu) + fabs(hx) + fabs(__dmul_rn(b, omv)) + fabs(__dmul_rn(b, lv)));
+  if (fabs(__dadd_rn(lu, -rhs)) >= band) return lu < rhs;
+  ++guard;
+  const double luc = cr_log(u), lvc = cr_log(v);
+  return luc < __dadd_rn(hx, __dmul_rn(b, __dadd_rn(omv, lvc)));
+}
+// Johnk's test X + Y <= 1 with X = U^(1/a): the bandit's shapes are 1 + an integer count, so this branch only ever runs
+// with a = b = 1, where X = U and Y = V exactly (no pow at all).  Other shapes <= 1 cannot come from the class API; a
+// near-tie there is counted (it is decided with pow as it stands).
+__device__ __forceinline__ double johnk_pow(double u, double a) { return a == 1.0 ? u : pow(u, 1.0 / a); }
+__device__ __forceinline__ void johnk_guard(double xpy, double a, double b, int& guard) {
+  if ((a != 1.0 || b != 1.0) && fabs(__dadd_rn(xpy, -1.0)) < 0x1p-40) ++guard;
 }
 
 __device__ double np_gauss(DevMt& g) {
@@ -187,29 +277,32 @@ __device__ double np_std_gamma(DevMt& g, double shape) {
     const double u = mt_double(g);
     const double x2 = __dmul_rn(x, x);
     if (u < __dadd_rn(1.0, -__dmul_rn(__dmul_rn(0.0331, x2), x2))) return __dmul_rn(b, v);
-    // log(U) < 0.5*X*X + b*(1 - V + log(V)), evaluated without fused multiply-add like the C reference
-    const double rhs = __dadd_rn(__dmul_rn(__dmul_rn(0.5, x), x), __dmul_rn(b, __dadd_rn(__dadd_rn(1.0, -v), log(v))));
-    if (log(u) < rhs) return __dmul_rn(b, v);
+    if (mt_accept(u, x, v, b, g.guard)) return __dmul_rn(b, v);
   }
 }
 
-__device__ double np_beta(DevMt& g, double a, double b) {
+// rk_beta draw by draw: the variate is num / den
+__device__ void np_beta_parts(DevMt& g, double a, double b, double* num, double* den) {
+  *den = 1.0;
   if (a <= 1.0 && b <= 1.0) {
     for (;;) {
       const double u = mt_double(g), v = mt_double(g);
-      const double x = pow(u, 1.0 / a), y = pow(v, 1.0 / b);
+      const double x = johnk_pow(u, a), y = johnk_pow(v, b);
       const double xpy = __dadd_rn(x, y);
+      johnk_guard(xpy, a, b, g.guard);
       if (xpy <= 1.0 && __dadd_rn(u, v) > 0.0) {
-        if (xpy > 0) return x / xpy;
+        if (xpy > 0) { *num = x; *den = xpy; return; }
         double lx = log(u) / a, ly = log(v) / b;
         const double lm = lx > ly ? lx : ly;
         lx -= lm; ly -= lm;
-        return exp(lx - log(__dadd_rn(exp(lx), exp(ly))));
+        *num = exp(lx - log(__dadd_rn(exp(lx), exp(ly))));
+        return;
       }
     }
   }
   const double ga = np_std_gamma(g, a), gb = np_std_gamma(g, b);
-  return ga / __dadd_rn(ga, gb);
+  *num = ga;
+  *den = __dadd_rn(ga, gb);
 }
 
 // ---- Thompson sampling: the NumPy stream through a look-ahead window ------------------------------------------
@@ -229,11 +322,12 @@ struct NpWindow {
   int head;          // doubles consumed from the window
   int has_gauss;
   double gauss;
-  int fail;          // a single beta draw ran past the window (probability ~1e-20): reported to the host
+  int fail;          // a single beta draw ran past the window (probability ~1e-20): that arm is redrawn draw by draw
   double *U, *gret, *gcache, *E;
   uint8_t* ok;
   short* nok;        // nok[i] = first position j >= i, j = i mod 2, whose polar attempt succeeds (kWinD: none in reach)
   int have_E;
+  int guard;         // guard-band hits of the draws made through this (copy of the) window
 };
 
 __device__ __forceinline__ uint32_t* win_blk(const NpWindow& w, int which) { return which ? w.blk1 : w.blk0; }
@@ -378,8 +472,7 @@ __device__ __forceinline__ double win_std_gamma(NpWindow& w, double shape, doubl
     if (w.fail) return 0.0;
     const double x2 = __dmul_rn(x, x);
     if (u < __dadd_rn(1.0, -__dmul_rn(__dmul_rn(0.0331, x2), x2))) return __dmul_rn(b, v);
-    const double rhs = __dadd_rn(__dmul_rn(__dmul_rn(0.5, x), x), __dmul_rn(b, __dadd_rn(__dadd_rn(1.0, -v), log(v))));
-    if (log(u) < rhs) return __dmul_rn(b, v);
+    if (mt_accept(u, x, v, b, w.guard)) return __dmul_rn(b, v);
   }
 }
 
@@ -391,8 +484,9 @@ __device__ __forceinline__ void win_beta(NpWindow& w, double a, double b, double
     for (;;) {
       const double u = win_double(w), v = win_double(w);
       if (w.fail) return;
-      const double x = pow(u, 1.0 / a), y = pow(v, 1.0 / b);
+      const double x = johnk_pow(u, a), y = johnk_pow(v, b);
       const double xpy = __dadd_rn(x, y);
+      johnk_guard(xpy, a, b, w.guard);
       if (xpy <= 1.0 && __dadd_rn(u, v) > 0.0) {
         if (xpy > 0) { *num = x; *den = xpy; return; }
         double lx = log(u) / a, ly = log(v) / b;
@@ -408,6 +502,34 @@ __device__ __forceinline__ void win_beta(NpWindow& w, double a, double b, double
   *den = __dadd_rn(ga, gb);
 }
 
+// One beta draw taken draw by draw from the committed stream position, for the arm whose draw outran the look-ahead
+// window (or on request, SB_ROUTER_OPT_DEBUG_FALLBACK_PERIOD).  `w` holds the state before that arm; on return it is
+// the state after it, and the tables must be rebuilt.  Called by warp 0 with all lanes in step.
+__device__ void win_fallback_beta(NpWindow& w, double a, double b, double* num, double* den) {
+  const int lane = threadIdx.x & 31;
+  int p = w.pos + 2 * w.head;
+  if (p >= MT_N) {  // the committed position lies in the next block
+    if (!w.next_valid) {
+      for (int i = lane; i < MT_N; i += 32) win_blk(w, w.cur ^ 1)[i] = win_blk(w, w.cur)[i];
+      mt_regenerate(win_blk(w, w.cur ^ 1));
+    }
+    w.cur ^= 1;
+    w.next_valid = 0;
+    p -= MT_N;
+  }
+  __syncwarp();
+  DevMt g{win_blk(w, w.cur), p, w.has_gauss, w.gauss, 0, 0};
+  np_beta_parts(g, a, b, num, den);
+  if (g.regens) w.next_valid = 0;  // the block was regenerated in place: the other one no longer is its successor
+  w.pos = g.pos;
+  w.head = 0;
+  w.has_gauss = g.has_gauss;
+  w.gauss = g.gauss;
+  w.guard += g.guard;
+  w.fail = 0;
+  __syncwarp();
+}
+
 // T calls.  KIND 0 = epsilon-greedy, 1 = Thompson (a template parameter so that the epsilon-greedy instance does not carry
 // the Thompson window code and its registers).  reward_mode -1: route only.
 template <int KIND>
@@ -415,7 +537,7 @@ __global__ void __launch_bounds__(kRouterThreads)
 router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long T,
                   const long long* __restrict__ rows, const float* __restrict__ reward,
                   const float* __restrict__ arm_p, int reward_mode, int* __restrict__ decisions, int forced_arm,
-                  double forced_reward, long long forced_rows) {
+                  double forced_reward, long long forced_rows, int dbg_fallback_period) {
   constexpr int kind = KIND;
   __shared__ uint32_t s_py[MT_N], s_np[MT_N], s_np2[MT_N];
   __shared__ double s_U[kWinD + 2], s_gret[kWinD], s_gcache[kWinD], s_E[kWinD];
@@ -450,8 +572,9 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
     s_tries[j] = st->tries[j];
     s_val[j] = st->tries[j] ? (double)st->succ[j] / (double)st->tries[j] : 0.0;
   }
-  DevMt py{s_py, st->py.pos, 0, 0.0};
-  DevMt np{s_np, st->np.pos, st->np.has_gauss, st->np.gauss};
+  DevMt py{s_py, st->py.pos, 0, 0.0, 0, 0};
+  DevMt np{s_np, st->np.pos, st->np.has_gauss, st->np.gauss, 0, 0};
+  long long n_fallback = 0, n_draws = 0;
   int best = st->best;
   const bool tab = kind == 1 && n <= kTabArms;
   if (tab)
@@ -462,7 +585,7 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
     }
   __syncwarp();
   // Thompson: the NumPy stream is read through a window (committed position = np.pos at entry)
-  NpWindow win{s_np, s_np2, 0, 0, np.pos, 0, np.has_gauss, np.gauss, 0, s_U, s_gret, s_gcache, s_E, s_ok, s_nok, 0};
+  NpWindow win{s_np, s_np2, 0, 0, np.pos, 0, np.has_gauss, np.gauss, 0, s_U, s_gret, s_gcache, s_E, s_ok, s_nok, 0, 0};
   const bool windowed = kind == 1 && forced_arm < 0;
   // room one beta draw may need: two gammas, each a few doubles per trial; a refill is forced below this margin
   constexpr int kArmMargin = 48;
@@ -499,6 +622,14 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
           if (!win_built || kWinD - win.head < kArmMargin) {
             np_window_build(win, unit, &s_cmd);
             win_built = 1;
+          }
+          if (dbg_fallback_period > 0 && (n_draws + done) % dbg_fallback_period == dbg_fallback_period - 1) {
+            const double a = (double)(1 + s_succ[done]), b = (double)(1 + s_tries[done] - s_succ[done]);
+            double num, den;
+            win_fallback_beta(win, a, b, &num, &den);
+            if (lane == 0) { s_num[done] = num; s_den[done] = den; }
+            ++n_fallback; ++done; win_built = 0;
+            continue;
           }
           const int D = min(n - done, 32);
           int p = win.head, f = win.has_gauss, gq = -1;   // lane 0: the actual state
@@ -544,6 +675,7 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
           lw.has_gauss = flag0;
           lw.gauss = g_in;
           lw.fail = 0;
+          lw.guard = 0;
           const int j = done + lane;
           double num = 0.0, den = 1.0;
           if (valid) {
@@ -558,8 +690,22 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
                            (lane == 0 || (pe_head == p && pe_flag == flag0 && (!flag0 || pe_bits == __double_as_longlong(g_in))));
           const unsigned bal = __ballot_sync(0xffffffffu, okl);
           const int k = bal == 0xffffffffu ? 32 : __ffs((int)~bal) - 1;  // accepted lanes: 0 .. k-1
-          if (k == 0) { win.fail = 1; break; }  // the first lane itself ran out of window
+          if (k == 0) {
+            // the first lane itself ran out of window: that arm is drawn draw by draw from the committed position
+            const double a = (double)(1 + s_succ[done]), b = (double)(1 + s_tries[done] - s_succ[done]);
+            double fnum, fden;
+            win_fallback_beta(win, a, b, &fnum, &fden);
+            if (lane == 0) { s_num[done] = fnum; s_den[done] = fden; }
+            ++n_fallback; ++done; win_built = 0;
+            continue;
+          }
           if (lane < k) { s_num[j] = num; s_den[j] = den; }
+          {
+            int gh = lane < k ? lw.guard : 0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) gh += __shfl_xor_sync(0xffffffffu, gh, o);
+            win.guard += gh;
+          }
           win.head = __shfl_sync(0xffffffffu, e_head, k - 1);
           win.has_gauss = __shfl_sync(0xffffffffu, e_flag, k - 1);
           win.gauss = __longlong_as_double(__shfl_sync(0xffffffffu, e_bits, k - 1));
@@ -573,12 +719,22 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
           }
           const double a = (double)(1 + s_succ[j]), b = (double)(1 + s_tries[j] - s_succ[j]);
           double num, den;
-          win_beta(win, a, b, -1.0, -1.0, &num, &den);
+          const int h0 = win.head, f0 = win.has_gauss, g0 = win.guard;
+          const double c0 = win.gauss;
+          const bool force = dbg_fallback_period > 0 && (n_draws + j) % dbg_fallback_period == dbg_fallback_period - 1;
+          if (!force) win_beta(win, a, b, -1.0, -1.0, &num, &den);
+          if (force || win.fail) {
+            win.head = h0; win.has_gauss = f0; win.gauss = c0; win.guard = g0;
+            win_fallback_beta(win, a, b, &num, &den);
+            ++n_fallback; win_built = 0;
+          }
           const double v = num / den;
+          if (lane == 0 && t == T - 1) st->last_values[j] = v;
           if (j == 0 || v > top) { top = v; arm = j; }
         }
       }
-      if (tab && !win.fail) {
+      n_draws += n;
+      if (tab) {
         // the n divisions in parallel, then the same first-maximum scan
         __syncwarp();
         for (int j = lane; j < n; j += 32) s_num[j] = s_num[j] / s_den[j];
@@ -587,12 +743,8 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
           const double v = s_num[j];
           if (j == 0 || v > top) { top = v; arm = j; }
         }
-      }
-      if (win.fail) {
-        // one beta draw needed more than kArmMargin doubles (probability ~1e-20): this and the remaining calls are
-        // reported as -1 and the state is left at the last completed call's feedback
-        for (long long u = t + lane; u < T; u += 32) decisions[u] = -1;
-        break;
+        if (t == T - 1)
+          for (int j = lane; j < n; j += 32) st->last_values[j] = s_num[j];
       }
     }
     if (lane == 0 && forced_arm < 0) decisions[t] = arm;
@@ -649,7 +801,7 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
     router_bar();
   }
   const uint32_t* np_blk = s_np;
-  if (windowed && win_built) {
+  if (windowed && (win_built || n_fallback > 0)) {
     // commit the consumed part of the window: the state a draw-by-draw generator would be in
     int p = win.pos + 2 * win.head;
     if (p > MT_N) {
@@ -674,6 +826,8 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
     st->np.has_gauss = np.has_gauss;
     st->np.gauss = np.gauss;
     st->best = best;
+    st->guard_hits += (long long)win.guard + np.guard;
+    st->fallbacks += n_fallback;
   }
 }
 
@@ -683,6 +837,8 @@ struct sb_router {
   int kind, n;
   double epsilon;
   RouterState* d_state;
+  int dbg_fallback_period;
+  int* h_decision;  // pinned, device-visible: the kernel of sb_router_route writes the decision straight to the host
 };
 
 extern "C" int32_t sb_router_create(sb_router_t** out, int32_t kind, int32_t n_branches, double epsilon, int64_t seed,
@@ -726,13 +882,15 @@ extern "C" int32_t sb_router_create(sb_router_t** out, int32_t kind, int32_t n_b
       hs->best = (int)r;
     }
   }
-  sb_router* h = new sb_router{kind, n_branches, epsilon, nullptr};
+  sb_router* h = new sb_router{kind, n_branches, epsilon, nullptr, 0, nullptr};
   cudaError_t e = cudaMalloc(&h->d_state, sizeof(RouterState));
+  if (e == cudaSuccess) e = cudaHostAlloc(&h->h_decision, sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable);
   if (e == cudaSuccess) e = cudaMemcpy(h->d_state, hs, sizeof(RouterState), cudaMemcpyHostToDevice);
   delete hs;
   if (e != cudaSuccess) {
     sb::set_error("sb_router_create: %s", cudaGetErrorString(e));
     if (h->d_state) cudaFree(h->d_state);
+    if (h->h_decision) cudaFreeHost(h->h_decision);
     delete h;
     return SB_ERR_CUDA;
   }
@@ -743,6 +901,7 @@ extern "C" int32_t sb_router_create(sb_router_t** out, int32_t kind, int32_t n_b
 extern "C" int32_t sb_router_destroy(sb_router_t* h) {
   if (!h) return SB_OK;
   cudaFree(h->d_state);
+  cudaFreeHost(h->h_decision);
   delete h;
   return SB_OK;
 }
@@ -759,11 +918,12 @@ extern "C" int32_t sb_router_run(sb_router_t* h, int64_t T, const int64_t* d_row
   if (h->kind == SB_ROUTER_THOMPSON)
     router_run_kernel<1><<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, (long long)T,
                                                                         (const long long*)d_rows_per_call, d_reward,
-                                                                        d_arm_p, reward_mode, d_decisions, -1, 0.0, 0);
+                                                                        d_arm_p, reward_mode, d_decisions, -1, 0.0, 0,
+                                                                        h->dbg_fallback_period);
   else
     router_run_kernel<0><<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, (long long)T,
                                                             (const long long*)d_rows_per_call, d_reward, d_arm_p,
-                                                            reward_mode, d_decisions, -1, 0.0, 0);
+                                                            reward_mode, d_decisions, -1, 0.0, 0, 0);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }
@@ -774,10 +934,10 @@ extern "C" int32_t sb_router_feedback(sb_router_t* h, int32_t arm, int64_t rows,
   SB_REQUIRE(rows >= 1, SB_ERR_INVALID, "sb_router_feedback: rows must be >= 1 (reference divides by tries)");
   if (h->kind == SB_ROUTER_THOMPSON)
     router_run_kernel<1><<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, 1, nullptr, nullptr,
-                                                                        nullptr, 0, nullptr, arm, reward, (long long)rows);
+                                                                        nullptr, 0, nullptr, arm, reward, (long long)rows, 0);
   else
     router_run_kernel<0><<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, 1, nullptr, nullptr, nullptr, 0,
-                                                            nullptr, arm, reward, (long long)rows);
+                                                            nullptr, arm, reward, (long long)rows, 0);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }
@@ -829,5 +989,53 @@ extern "C" int32_t sb_router_set_state(sb_router_t* h, const int64_t* in, uintpt
   if (e == cudaSuccess) e = cudaStreamSynchronize(st);
   delete hs;
   if (e != cudaSuccess) { sb::set_error("sb_router_set_state: %s", cudaGetErrorString(e)); return SB_ERR_CUDA; }
+  return SB_OK;
+}
+
+extern "C" int32_t sb_router_set_option(sb_router_t* h, int32_t option, int64_t value) {
+  SB_REQUIRE(h, SB_ERR_INVALID, "sb_router_set_option: null handle");
+  SB_REQUIRE(option == SB_ROUTER_OPT_DEBUG_FALLBACK_PERIOD && value >= 0 && value <= 0x7fffffff, SB_ERR_INVALID,
+             "sb_router_set_option: unknown option %d or bad value", option);
+  h->dbg_fallback_period = (int)value;
+  return SB_OK;
+}
+
+extern "C" int32_t sb_router_counters(sb_router_t* h, int64_t* out2, uintptr_t stream) {
+  SB_REQUIRE(h && out2, SB_ERR_INVALID, "sb_router_counters: bad arguments");
+  long long v[2];
+  cudaStream_t st = (cudaStream_t)stream;
+  SB_CUDA(cudaMemcpyAsync(v, &h->d_state->guard_hits, sizeof v, cudaMemcpyDeviceToHost, st));
+  SB_CUDA(cudaStreamSynchronize(st));
+  out2[0] = v[0];
+  out2[1] = v[1];
+  return SB_OK;
+}
+
+// route() of the class API: one call, the decision written by the kernel into pinned host memory (no device buffer, no
+// copy), then a stream synchronisation.
+extern "C" int32_t sb_router_route(sb_router_t* h, int32_t* h_out, uintptr_t stream) {
+  SB_REQUIRE(h && h_out, SB_ERR_INVALID, "sb_router_route: bad arguments");
+  SB_REQUIRE(!(h->kind == SB_ROUTER_EPSILON_GREEDY && h->n < 2), SB_ERR_INVALID,
+             "epsilon-greedy needs >= 2 branches to explore (reference raises IndexError on random.choice([]))");
+  int* d_dec = nullptr;
+  SB_CUDA(cudaHostGetDevicePointer((void**)&d_dec, h->h_decision, 0));
+  if (h->kind == SB_ROUTER_THOMPSON)
+    router_run_kernel<1><<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, 1, nullptr, nullptr,
+                                                                        nullptr, -1, d_dec, -1, 0.0, 0,
+                                                                        h->dbg_fallback_period);
+  else
+    router_run_kernel<0><<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, 1, nullptr, nullptr, nullptr, -1,
+                                                            d_dec, -1, 0.0, 0, 0);
+  SB_LAUNCH_CHECK();
+  SB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  *h_out = *(volatile int*)h->h_decision;
+  return SB_OK;
+}
+
+extern "C" int32_t sb_router_last_values(sb_router_t* h, double* h_values, uintptr_t stream) {
+  SB_REQUIRE(h && h_values, SB_ERR_INVALID, "sb_router_last_values: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  SB_CUDA(cudaMemcpyAsync(h_values, h->d_state->last_values, sizeof(double) * h->n, cudaMemcpyDeviceToHost, st));
+  SB_CUDA(cudaStreamSynchronize(st));
   return SB_OK;
 }

@@ -29,7 +29,7 @@ class OutlierMahalanobisFeedbackB200(OutlierMahalanobisB200):
         self._last_score = None
 
     # ------------------------------------------------------------------ reference API
-    def send_feedback(self, X, feature_names, reward, truth):
+    def send_feedback(self, X, feature_names, reward, truth, routing=None):
         """OutlierMahalanobis.py:34-66: the labels `truth` belong to the rows of the last predict / transform_input."""
         import torch
 

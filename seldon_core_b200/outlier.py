@@ -47,8 +47,10 @@ class OutlierMahalanobisB200(object):
         self.prediction_meta = self._get_preds(X)
         return X
 
-    def send_feedback(self, X, feature_names, reward, truth):
-        return []  # L154-165
+    def send_feedback(self, X, feature_names, reward, truth, routing=None):
+        # L154-165.  `routing` is how the wrapper passes the request's routing (user_model.py:308-313); the detector has
+        # no use for it.
+        return []
 
     def tags(self):
         try:
@@ -218,7 +220,7 @@ class OutlierMahalanobisB200(object):
                     raw = torch.from_numpy(np.ascontiguousarray(Xn)).to(dev, non_blocking=True)
                     Xd = torch.empty(Xn.shape, dtype=torch.float32, device=dev)
                     with torch.cuda.device(dev):
-                        _cabi.check(_cabi.lib().sb_unpack_tensor_f64(raw.data_ptr(), 0, Xn.shape[0], Xn.shape[1], None,
+                        _cabi.check(_cabi.lib().sb_unpack_tensor_f64(raw.data_ptr(), 8 * Xn.size, 0, Xn.shape[0], Xn.shape[1], None,
                                                                      None, Xd.data_ptr(), Xn.shape[1],
                                                                      torch.cuda.current_stream().cuda_stream))
                 else:
@@ -262,7 +264,7 @@ class OutlierMahalanobisB200(object):
         import torch
 
         need = ctypes.c_uint64()
-        _cabi.check(_cabi.lib().sb_maha_workspace_bytes(self._h, rows, ctypes.byref(need)))
+        _cabi.check(_cabi.lib().sb_maha_workspace_bytes(self._h, max(int(rows), 1), ctypes.byref(need)))
         if self._ws is None or self._ws.numel() < need.value:
             self._ws = torch.empty(int(need.value), dtype=torch.uint8, device=self._device)
         return self._ws

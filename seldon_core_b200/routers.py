@@ -103,16 +103,24 @@ class _RouterBase(object):
 
         with self._lock:
             h = self._handle()
-            out = torch.empty(1, dtype=torch.int32, device=self._device)
+            out = ctypes.c_int32()
             with torch.cuda.device(self._device):
-                _cabi.check(_cabi.lib().sb_router_run(h, 1, None, None, None, -1, out.data_ptr(), self._stream()))
-            branch = int(out.item())
-            if branch < 0:
-                raise SeldonB200Error("router: a sampling draw overran its look-ahead window; router state is invalid",
-                                      status_code=500)
-            if self.history:
+                _cabi.check(_cabi.lib().sb_router_route(h, ctypes.byref(out), self._stream()))
+            branch = int(out.value)
+            if self.history:  # EpsilonGreedy.py:99-101, ThompsonSampling.py:88-90
                 self.branch_history.append(branch)
+                self.value_history.append(list(self.branch_values))
             return branch
+
+    def counters(self):
+        """{guard_hits, fallbacks}: comparisons of the legacy gamma sampler decided again with correctly rounded
+        logarithms, and beta draws taken draw by draw outside the look-ahead window (include/sb200.h)."""
+        import torch
+
+        out = (ctypes.c_int64 * 2)()
+        with torch.cuda.device(self._device):
+            _cabi.check(_cabi.lib().sb_router_counters(self._handle(), out, self._stream()))
+        return {"guard_hits": int(out[0]), "fallbacks": int(out[1])}
 
     def send_feedback(self, features, feature_names, *args, routing=None, **kwargs):
         if routing is None and len(args) == 3:  # component style: (routing, reward, truth)
@@ -210,6 +218,16 @@ class ThompsonSamplingB200(_RouterBase):
 
     def __init__(self, n_branches=None, verbose=False, seed=None, history=False, branch_names=None, device=None):
         self._init_common(n_branches, 0.0, None, verbose, seed, history, branch_names, device)
+
+    @property
+    def branch_values(self):
+        """The beta samples of the last route (ThompsonSampling.py:81-82); zeros before the first one (L65)."""
+        import torch
+
+        v = np.zeros(self.n_branches)
+        with torch.cuda.device(self._device if self._device is not None else 0):
+            _cabi.check(_cabi.lib().sb_router_last_values(self._handle(), v.ctypes.data, self._stream()))
+        return v.tolist()
 
     @property
     def models_beta_params(self):

@@ -99,3 +99,25 @@ def test_ndarray_ring_kernel_rejects_bad_tag_in_a_late_chunk():
     wire[500 * row_bytes] = 0x12  # row header tag
     with pytest.raises(SeldonB200Error):
         codec.decode_ndarray(bytes(wire), 8)
+
+
+def test_decode_tensor_rejects_shape_payload_mismatch():
+    """A Tensor whose shape claims more values than the message carries must raise, as the reference does on the
+    reshape (utils.py:169), both in the host parser and at the C ABI (no out-of-bounds read on the device)."""
+    import torch
+
+    from seldon_core_b200 import _cabi
+
+    good = ocodec.encode_tensor(np.arange(6.0).reshape(2, 3))
+    lying = b"\x0a\x04\xe8\x07\xe8\x07" + b"\x12\x10" + b"\x00" * 16          # shape [1000, 1000], 16 bytes of values
+    for bad in (lying, good[:-8], good + b"\x00" * 8, good[:6]):
+        with pytest.raises(SeldonB200Error):
+            codec.decode_tensor(bad)
+    wire = torch.zeros(64, dtype=torch.uint8, device="cuda")
+    out = torch.empty((1000, 1000), dtype=torch.float32, device="cuda")
+    rc = _cabi.lib().sb_unpack_tensor_f64(wire.data_ptr(), wire.numel(), 8, 1000, 1000, None, None, out.data_ptr(), 1000,
+                                          torch.cuda.current_stream().cuda_stream)
+    assert rc == -1 and b"payload has 64" in _cabi.lib().sb_last_error()
+    rc = _cabi.lib().sb_unpack_tensor_f64(wire.data_ptr(), wire.numel(), 2 ** 63, 1, 1, None, None, out.data_ptr(), 1,
+                                          torch.cuda.current_stream().cuda_stream)
+    assert rc == -1

@@ -105,3 +105,52 @@ def test_thompson_window_paths_against_c_oracle(n, T, chunks):
     dec = np.concatenate(got)
     assert np.array_equal(dec, ref), "first mismatch at call %d" % int(np.flatnonzero(dec != ref)[0])
     assert r.branch_success == st[:n].tolist() and r.branch_tries == st[n:2 * n].tolist()
+
+
+@pytest.mark.parametrize("n,period", [(32, 1), (32, 7), (5, 3), (200, 11), (64, 64)])
+def test_thompson_draw_by_draw_fallback_keeps_the_decisions(n, period):
+    """A beta draw that outruns the look-ahead window is taken draw by draw from the committed stream position
+    (probability ~1e-20 per draw, so the test forces it on every `period`-th draw): decisions, bandit state and the
+    generator position afterwards must be those of the C oracle."""
+    T = 1500
+    p, u = synth.router_rewards(T, n)
+    ref, st = R.run_batched(1, n, 0.1, 5, 0, T, reward=u, reward_mode=R.REWARD_BERNOULLI, arm_p=p)
+    r = ThompsonSamplingB200(n_branches=n, seed=5)
+    _cabi.check(_cabi.lib().sb_router_set_option(r._handle(), _cabi.SB_ROUTER_OPT_DEBUG_FALLBACK_PERIOD, period))
+    a = r.run_batched(1000, u[:1000], reward_mode=_cabi.SB_REWARD_BERNOULLI, arm_p=p).cpu().numpy()
+    _cabi.check(_cabi.lib().sb_router_set_option(r._handle(), _cabi.SB_ROUTER_OPT_DEBUG_FALLBACK_PERIOD, 0))
+    b = r.run_batched(500, u[1000:], reward_mode=_cabi.SB_REWARD_BERNOULLI, arm_p=p).cpu().numpy()  # windowed again
+    dec = np.concatenate([a, b])
+    assert np.array_equal(dec, ref), "first mismatch at call %d" % int(np.flatnonzero(dec != ref)[0])
+    assert r.branch_success == st[:n].tolist() and r.branch_tries == st[n:2 * n].tolist()
+    c = r.counters()
+    assert c["fallbacks"] >= 1000 * n // period - 1
+    assert (dec >= 0).all()
+
+
+def test_history_and_branch_values_like_the_reference_classes():
+    """EpsilonGreedy.py:99-101 / ThompsonSampling.py:81-90: with history=True both branch_history and value_history grow
+    on every route; Thompson's branch_values are the beta samples of the last route (NumPy legacy stream)."""
+    class Feat:
+        shape = (1, 4)
+
+    t = ThompsonSamplingB200(n_branches=6, seed=9, history=True)
+    assert t.branch_values == [0.0] * 6
+    rs = np.random.RandomState(9)
+    params = [[1, 1] for _ in range(6)]
+    for step in range(40):
+        want = [rs.beta(a, b) for a, b in params]
+        arm = t.route(None, None)
+        assert arm == int(np.argmax(want))
+        assert t.branch_values == want            # bit-equal doubles
+        assert t.value_history[-1] == want and t.branch_history[-1] == arm
+        rew = 1.0 if step % 3 else 0.0
+        t.send_feedback(Feat, None, arm, rew, None)
+        params[arm][0] += int(rew)
+        params[arm][1] += 1 - int(rew)
+    assert t.models_beta_params == params
+    e = EpsilonGreedyB200(n_branches=4, epsilon=0.3, seed=2, history=True)
+    for step in range(20):
+        arm = e.route(None, None)
+        assert e.value_history[-1] == e.branch_values and len(e.branch_history) == step + 1
+        e.send_feedback(Feat, None, arm, float(step % 2), None)

@@ -101,14 +101,17 @@ def _gloo_worker(rank, world, port, total_rows, d, out):
         dist.destroy_process_group()
 
 
-def test_gloo_two_rank_stats_exchange_matches_single_call():
+@pytest.mark.parametrize("total_rows", [101, 1])
+def test_gloo_two_rank_stats_exchange_matches_single_call(total_rows):
     """World size 2 on CPU: the gathered per-shard (count, sum, Gram) records add up to the single-call statistics
-    and rank 1's prefix is rank 0's record (the only collective on the path)."""
+    and rank 1's prefix is rank 0's record (the only collective on the path).  With fewer rows than ranks the empty
+    rank contributes an all-zero record and still joins the collective (it used to fail before it, leaving the other
+    rank blocked in the all-gather)."""
     import torch.multiprocessing as mp
 
     from oracle.mahalanobis import MahalanobisLean
 
-    total_rows, d, world = 101, 5, 2
+    d, world = 5, 2
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
@@ -152,3 +155,20 @@ def test_json_ndarray_span_locates_the_value_without_parsing_numbers():
     for bad in (b'{"data":{"tensor":{"shape":[1],"values":[1]}}}', b'{"data":{"ndarray":[[1,2],[3,4]'):
         with pytest.raises(SeldonB200Error):
             codec.json_ndarray_span(bad)
+
+
+def test_tensor_header_parser_rejects_truncated_and_lying_payloads():
+    """shape [1000, 1000] with 16 bytes of values used to give a negative values offset."""
+    import numpy as np
+
+    from oracle import codec as ocodec
+    from seldon_core_b200 import codec
+    from seldon_core_b200.errors import SeldonB200Error
+
+    good = ocodec.encode_tensor(np.arange(6.0).reshape(2, 3))
+    shape, off = codec.parse_tensor_header(good)
+    assert shape == [2, 3] and off == len(good) - 48 == ocodec.tensor_values_offset((2, 3))
+    lying = b"\x0a\x04\xe8\x07\xe8\x07" + b"\x12\x10" + b"\x00" * 16
+    for bad in (lying, good[:-8], good + b"\x00" * 8, good[:6], good[:3], b"\x0a\x02\x02\x03"):
+        with pytest.raises(SeldonB200Error):
+            codec.parse_tensor_header(bad)

@@ -63,7 +63,7 @@ def codec_bench():
     wire = torch.empty(rows * cols * 8, dtype=torch.uint8, device="cuda")
     out = torch.empty_like(x)
     f_pack = lambda: _cabi.check(L.sb_pack_tensor_f64(x.data_ptr(), 0, rows * cols, wire.data_ptr(), st))
-    f_unpack = lambda: _cabi.check(L.sb_unpack_tensor_f64(wire.data_ptr(), 0, rows, cols, None, None, out.data_ptr(), cols, st))
+    f_unpack = lambda: _cabi.check(L.sb_unpack_tensor_f64(wire.data_ptr(), wire.numel(), 0, rows, cols, None, None, out.data_ptr(), cols, st))
     best, med = timed(f_pack)
     emit("pack tensor fp32->f64 (4Mi x 64)", "values/s", rows * cols, 12 * rows * cols, best, med)
     best, med = timed(f_unpack)
