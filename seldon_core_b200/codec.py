@@ -6,6 +6,7 @@ Host-side mirror of the numeric branches of ``python/seldon_core/utils.py``: ``g
 (the packed doubles / the 11-byte ListValue records) is converted by libsb200.so on the GPU.
 """
 import re
+import threading
 
 import numpy as np
 
@@ -44,14 +45,32 @@ def _device(device):
     return torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
 
 
+_STAGING = {}  # device -> [pinned uint8 tensor, event of the last copy out of it]
+_STAGING_LOCK = threading.Lock()
+
+
 def _upload(wire, dev, offset_to_align):
-    """Copy wire bytes to the device so that byte `offset_to_align` lands on a 16-byte boundary."""
+    """Copy wire bytes to the device so that byte `offset_to_align` lands on a 16-byte boundary.  The bytes go through
+    one pinned staging buffer per device that grows to the largest payload seen and is reused (pinning memory per
+    request is a device-synchronising cudaHostAlloc); the copy out of it is awaited before the next payload is staged."""
     import torch
 
     pad = (-offset_to_align) % 16
-    host = torch.empty(pad + len(wire), dtype=torch.uint8).pin_memory()
-    host[pad:] = torch.frombuffer(memoryview(wire), dtype=torch.uint8)
-    return host.to(dev, non_blocking=True), pad
+    n = pad + len(wire)
+    with _STAGING_LOCK:
+        ent = _STAGING.get(dev)
+        if ent is None or ent[0].numel() < n:
+            if ent is not None:
+                ent[1].synchronize()
+            ent = [torch.empty(max(n, 1 << 16) * 5 // 4, dtype=torch.uint8).pin_memory(), torch.cuda.Event()]
+            _STAGING[dev] = ent
+        else:
+            ent[1].synchronize()
+        ent[0][pad:n].numpy()[:] = np.frombuffer(wire, dtype=np.uint8)
+        with torch.cuda.device(dev):
+            out = ent[0][:n].to(dev, non_blocking=True)
+            ent[1].record(torch.cuda.current_stream(dev))
+    return out, pad
 
 
 def parse_tensor_header(wire):
@@ -231,7 +250,7 @@ def decode_json_ndarray(payload, device=None):
     text = payload[start:end]
     dev = _device(device)
     L = _cabi.lib()
-    buf = torch.frombuffer(bytearray(text), dtype=torch.uint8).to(dev)
+    buf, _pad = _upload(text, dev, 0)
     ws = torch.empty((int(L.sb_json_workspace_bytes(len(text))) + 7) // 8, dtype=torch.int64, device=dev)
     counts = torch.zeros(4, dtype=torch.int64, device=dev)
     with torch.cuda.device(dev):

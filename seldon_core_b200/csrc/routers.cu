@@ -623,7 +623,10 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
             np_window_build(win, unit, &s_cmd);
             win_built = 1;
           }
-          if (dbg_fallback_period > 0 && (n_draws + done) % dbg_fallback_period == dbg_fallback_period - 1) {
+          // test knob: draws until the next one that is forced through the fallback (0 = this one)
+          const int dbg_left = dbg_fallback_period > 0
+                                   ? dbg_fallback_period - 1 - (int)((n_draws + done) % dbg_fallback_period) : 1 << 30;
+          if (dbg_left == 0) {
             const double a = (double)(1 + s_succ[done]), b = (double)(1 + s_tries[done] - s_succ[done]);
             double num, den;
             win_fallback_beta(win, a, b, &num, &den);
@@ -631,7 +634,7 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
             ++n_fallback; ++done; win_built = 0;
             continue;
           }
-          const int D = min(n - done, 32);
+          const int D = min(min(n - done, 32), dbg_left);
           int p = win.head, f = win.has_gauss, gq = -1;   // lane 0: the actual state
           {
             int cp = p, cf = f, cq = -1;  // the chase, identical in every lane

@@ -36,6 +36,7 @@ class OutlierMahalanobisB200(object):
         self._score_t = None
         self._flag_t = None
         self._options = {}
+        self._wire = None
 
     # ------------------------------------------------------------------ reference API
     def predict(self, X, feature_names=None):
@@ -72,6 +73,81 @@ class OutlierMahalanobisB200(object):
                 g("observation", self.n),
                 g("threshold", self.threshold),
             ]
+
+    # ------------------------------------------------------------------ raw hooks (bytes in -> bytes out)
+    def predict_raw(self, msg, shard=None):
+        """The hook the wrapper tries before anything else (seldon_methods.py:43-47, user_model.py:36-37): `msg` is a
+        serialised SeldonMessage (bytes, a pinned `wire.HostBuf`, a uint8 CPU tensor), a protobuf SeldonMessage object
+        (gRPC: re-serialised once) or the parsed REST dict.  The payload is decoded on the device, scored, and the
+        response (flags as the request's payload kind, `names: []`, meta with tags and the six gauges, puid echoed -
+        construct_response, utils.py:410-469) is encoded on the device.  Bytes-like in -> `wire.HostBuf` out (a view
+        of this instance's pinned response buffer, valid until the next raw call); protobuf object in -> an object of
+        the same class; dict in -> dict.  `shard=(ShardedMahalanobis, total_rows)` scores this rank's row block."""
+        return self._raw(msg, False, shard)
+
+    def transform_input_raw(self, msg, shard=None):
+        """As predict_raw for the transformer mode (seldon_methods.py:124-128): the response echoes the request's
+        `data` unchanged and carries the flags in `meta.tags["outlier-predictions"]` (CoreMahalanobis.py:54-65,
+        168-177), packed on the device."""
+        return self._raw(msg, True, shard)
+
+    def _raw(self, msg, transform, shard):
+        from . import wire
+
+        if isinstance(msg, dict):
+            return self._raw_json(msg, transform)
+        with self._lock:
+            if self._wire is None:
+                self._wire = wire.WireStage(self._pick_device())
+            st = self._wire
+            host = st.host_bytes(msg)
+            info = wire.parse_seldon_message(host.numpy())
+            X = st.decode_matrix(host, info)
+            if shard is not None:
+                _, flag = shard[0].score_shard(X, int(shard[1]))
+            else:
+                _, flag = self.score_device(X)
+            if transform:
+                self.prediction_meta = flag.cpu().numpy().astype(int)
+                off, ln = info["data"]
+                resp = wire.build_message(st, info["kind"], None, None, puid=info["puid"],
+                                          tags_dev={"outlier-predictions": flag}, metrics=self.metrics(),
+                                          data_raw=host.numpy()[off:off + ln])
+            else:
+                resp = wire.build_message(st, info["kind"], [], flag, puid=info["puid"], tags=self.tags(),
+                                          metrics=self.metrics())
+        if hasattr(msg, "SerializeToString"):
+            return type(msg).FromString(resp.tobytes())
+        return resp
+
+    def _raw_json(self, request, transform):
+        """REST: the body has already been parsed by json.loads (seldon_methods.py:53-57 -> construct_response_json,
+        utils.py:306-407): numeric data.tensor / data.ndarray only."""
+        d = request.get("data") or {}
+        if "tensor" in d:
+            X = np.array(d["tensor"]["values"], dtype=np.float64).reshape(d["tensor"]["shape"])
+        elif "ndarray" in d:
+            X = np.array(d["ndarray"], dtype=np.float64)
+        else:
+            raise SeldonB200Error("the request carries no data.tensor / data.ndarray payload")
+        names = d.get("names", [])
+        out = self.transform_input(X, names) if transform else self.predict(X, names)
+        out = np.asarray(out)
+        data = {}
+        if "tensor" in d:
+            data["tensor"] = {"values": out.ravel().tolist(), "shape": out.shape}
+        else:
+            data["ndarray"] = out.tolist()
+        data["names"] = list(names) if transform else []
+        resp = {"data": data, "meta": {}}
+        tags = self.tags()
+        if tags:
+            resp["meta"]["tags"] = tags
+        resp["meta"]["metrics"] = self.metrics()
+        puid = (request.get("meta") or {}).get("puid")
+        if puid:
+            resp["meta"]["puid"] = puid
+        return resp
 
     # ------------------------------------------------------------------ public attributes of the reference
     @property
@@ -349,6 +425,7 @@ class OutlierMahalanobisB200(object):
         self._score_t = None
         self._flag_t = None
         self._options = opts
+        self._wire = None
         self._restore = saved if d is not None else None
         self._restore_d = d
         self._fused = None

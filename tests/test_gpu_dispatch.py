@@ -35,7 +35,7 @@ def test_detector_through_client_predict_tags_metrics():
     want = ref.predict(X.astype(np.float64), names)
     assert isinstance(out, np.ndarray) and out.shape == (9000,) and np.array_equal(out, want)
     assert um.client_class_names(det, out) == []                       # 1-D result: no names (user_model.py:130-131)
-    assert um.client_custom_tags(det) == {}                            # tags() is None before transform_input
+    assert um.client_custom_tags(det) is None                          # as the reference's tags() before transform_input (L168-177)
     met = um.client_custom_metrics(det)                                # -> validate_metrics
     assert [m["key"] for m in met] == ["is_outlier", "outlier_score", "nb_outliers", "fraction_outliers", "observation",
                                        "threshold"]

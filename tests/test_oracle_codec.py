@@ -82,3 +82,56 @@ def test_reference_known_answers():
     assert codec.class_names(np.zeros((1, 2))) == ["t:0", "t:1"]
     assert codec.class_names(np.zeros(5)) == []
     assert codec.class_names(np.zeros((1, 2)), ["a", "b"]) == ["a", "b"]
+
+
+def test_response_framing_of_the_wire_module_equals_the_protobuf_runtime():
+    """Host side of seldon_core_b200/wire.py (no GPU): message parsing, metric and tag-value encoding against the
+    run-time built SeldonMessage classes of oracle/seldon_pb.py (proto/prediction.proto:14-82)."""
+    import numpy as np
+
+    from oracle import seldon_pb
+    from seldon_core_b200 import wire
+    from seldon_core_b200.errors import SeldonB200Error
+
+    C = seldon_pb.classes()
+    X = np.arange(12.0).reshape(3, 4)
+    for kind in ("tensor", "ndarray"):
+        req = seldon_pb.request_message(X, kind, ["a", "b", "c", "d"], puid="p")
+        raw = req.SerializeToString()
+        info = wire.parse_seldon_message(raw)
+        assert info["puid"] == "p" and info["names"] == ["a", "b", "c", "d"] and info["kind"] == kind
+        off, ln = info["payload"]
+        sub = getattr(req.data, kind).SerializeToString()
+        assert raw[off:off + ln] == sub
+        off, ln = info["data"]
+        assert raw[off:off + ln] == req.data.SerializeToString()
+    metrics = [{"type": "GAUGE", "key": "is_outlier", "value": np.float64(0.25)}, {"type": "COUNTER", "key": "c", "value": 3},
+               {"type": "TIMER", "key": "t", "value": 0.0}, {"type": "GAUGE", "key": "", "value": -0.0}]
+    tags = {"outlier-predictions": [0, 1, 1, 0]}
+    want = seldon_pb.construct_response(False, seldon_pb.request_message(X), np.array([0, 1, 0]), tags=tags, metrics=metrics)
+    meta = want.meta.SerializeToString()
+    kb, vb = b"outlier-predictions", wire.encode_value_host(tags["outlier-predictions"])
+    entry = b"\x0a" + bytes([len(kb)]) + kb + b"\x12" + bytes([len(vb)]) + vb
+    assert meta == b"\x12" + bytes([len(entry)]) + entry + wire.encode_metrics_host(metrics)
+    for v in (1.5, "txt", True, [1, "a", [2.0]], None):
+        from google.protobuf import struct_pb2
+
+        ref = struct_pb2.Value()
+        if v is None:
+            ref.null_value = 0
+        elif isinstance(v, list):
+            ref.list_value.extend(v)
+        elif isinstance(v, bool):
+            ref.bool_value = v
+        elif isinstance(v, str):
+            ref.string_value = v
+        else:
+            ref.number_value = v
+        assert wire.encode_value_host(v) == ref.SerializeToString(), v
+    lst = C["SeldonMessageList"](seldonMessages=[seldon_pb.request_message(X), seldon_pb.request_message(X + 1)])
+    raw = lst.SerializeToString()
+    parts = wire.split_message_list(raw)
+    assert [raw[o:o + n] for o, n in parts] == [m.SerializeToString() for m in lst.seldonMessages]
+    for bad in (b"\x1a\x05\x12\x03", b"\x1a\xff", C["SeldonMessage"](binData=b"x").SerializeToString()):
+        with pytest.raises(SeldonB200Error):
+            wire.parse_seldon_message(bad)
