@@ -233,6 +233,15 @@ int32_t sb_router_counters(sb_router_t* h, int64_t* out2, uintptr_t stream);
 #define SB_ROUTER_OPT_DEBUG_FALLBACK_PERIOD 1
 int32_t sb_router_set_option(sb_router_t* h, int32_t option, int64_t value);
 
+/* RANDOM_ABTEST, the engine's built-in two-way router: replaces
+ * engine/src/main/java/io/seldon/engine/predictors/RandomABTestUnit.java:29-59 - `new Random(1337)` (L31),
+ * `rand.nextFloat()` per call (L45), branch 0 iff nextFloat() <= ratioA (L52) - batched: T calls per launch, the
+ * java.util.Random stream consumed in parallel by jump-ahead (the generator is an affine map modulo 2^48).
+ * d_state2: two device words; word 0 is the generator state (start: sb_abtest_initial_state(1337)), advanced by T
+ * calls when the launch completes; word 1 is scratch. */
+uint64_t sb_abtest_initial_state(int64_t seed);
+int32_t sb_abtest_route(uint64_t* d_state2, float ratio_a, int64_t T, int32_t* d_decisions, uintptr_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -62,3 +62,49 @@ class ShardedMahalanobis(object):
         self.det.pass1_device(X_local, local)
         all_stats = gather_stats(local, self.group)
         return self.det.finish_device(X_local, all_stats, self.world, self.rank, int(total_rows), row0)
+
+
+class ShardedRouter(object):
+    """The bandit routers are sequential and are not sharded: every rank holds the requests of its row
+    block, rank 0 holds the router.  Per batch of requests: the per-request reward inputs (one float per rank-local
+    request) are gathered to rank 0, which plays all requests of all ranks in rank order in one `run_batched` launch,
+    and the decisions are broadcast back; every rank returns the decisions of its own requests.  The call sequence it
+    serves is route (seldon_methods.py:196-243) followed by send_feedback (L59-103) per request.
+
+    `router` is an EpsilonGreedyB200 / ThompsonSamplingB200 on rank 0 (ignored elsewhere) or any callable
+    `(T, rewards float32[T]) -> int32[T]` (the gloo tests pass the C oracle)."""
+
+    def __init__(self, router, group=None, reward_mode=2, arm_p=None):
+        import torch.distributed as dist
+
+        self.router, self.group = router, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.reward_mode, self.arm_p = reward_mode, arm_p
+
+    def play(self, local_rewards):
+        """local_rewards: float32 tensor [m], one entry per request of this rank (with reward mode BERNOULLI the
+        uniform u_t that decides success against the chosen arm's probability).  Returns int32 [m]."""
+        import torch
+        import torch.distributed as dist
+
+        dev = local_rewards.device
+        m = torch.tensor([local_rewards.numel()], dtype=torch.int64, device=dev)
+        counts = torch.empty(self.world, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(counts, m, group=self.group)
+        counts = counts.cpu().tolist()
+        mmax, total = max(counts), sum(counts)
+        padded = torch.zeros(max(mmax, 1), dtype=torch.float32, device=dev)
+        padded[:local_rewards.numel()] = local_rewards.to(torch.float32)
+        gathered = [torch.empty_like(padded) for _ in range(self.world)] if self.rank == 0 else None
+        dist.gather(padded, gathered, dst=0, group=self.group)
+        decisions = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
+        if self.rank == 0 and total > 0:
+            rew = torch.cat([g[:c] for g, c in zip(gathered, counts)])
+            if callable(self.router) and not hasattr(self.router, "run_batched"):
+                dec = self.router(total, rew)
+            else:
+                dec = self.router.run_batched(total, rew, reward_mode=self.reward_mode, arm_p=self.arm_p)
+            decisions[:total] = torch.as_tensor(dec, dtype=torch.int32, device=dev)
+        dist.broadcast(decisions, src=0, group=self.group)
+        lo = sum(counts[:self.rank])
+        return decisions[lo:lo + counts[self.rank]]

@@ -172,3 +172,55 @@ def test_tensor_header_parser_rejects_truncated_and_lying_payloads():
     for bad in (lying, good[:-8], good + b"\x00" * 8, good[:6], good[:3], b"\x0a\x02\x02\x03"):
         with pytest.raises(SeldonB200Error):
             codec.parse_tensor_header(bad)
+
+
+def _gloo_router_worker(rank, world, port, out):
+    import torch
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import routers as R
+        from seldon_core_b200 import synth
+
+        T = 1000
+        p, u = synth.router_rewards(T, 8)
+        counts = [400, 0, 600] if world == 3 else [123, 877]
+        lo = sum(counts[:rank])
+
+        def play(total, rewards):        # rank 0 only: the C oracle stands in for the device router
+            dec, _ = R.run_batched(0, 8, 0.1, 3, 0, total, reward=rewards.numpy(), reward_mode=R.REWARD_BERNOULLI, arm_p=p)
+            return dec
+
+        sr = sdist.ShardedRouter(play)
+        mine = sr.play(torch.from_numpy(u[lo:lo + counts[rank]]))
+        out.put((rank, mine.numpy().tolist()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gloo_router_reward_gather_and_decision_broadcast(world):
+    """SURVEY 8(e), last bullet: rewards gathered to rank 0, the sequential bandit played there over all ranks'
+    requests in rank order, decisions broadcast; a rank without requests still takes part."""
+    import torch.multiprocessing as mp
+
+    from oracle import routers as R
+    from seldon_core_b200 import synth
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_router_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    p_arm, u = synth.router_rewards(1000, 8)
+    want, _ = R.run_batched(0, 8, 0.1, 3, 0, 1000, reward=u, reward_mode=R.REWARD_BERNOULLI, arm_p=p_arm)
+    got = sum((res[r] for r in range(world)), [])
+    assert got == want.tolist()
