@@ -177,7 +177,8 @@ int32_t sb_maha_last_batch_sums(sb_maha_t* h, int64_t* n_flagged, double* score_
  * Synchronises the stream. */
 int32_t sb_maha_kernel_times(sb_maha_t* h, float* out_ms5, uintptr_t stream);
 /* diagnostics: out8 = { first open sub-segment, gate row, flagged rows, Jacobi sweeps, batch rows,
- * sub-segments, sub-segment length, 0 } of the last batch.  Synchronises. */
+ * sub-segments, sub-segment length, subspace-iteration count (> 0: accepted, < 0: not accepted and the Jacobi solver
+ * ran, 0: not attempted) } of the last batch.  Synchronises. */
 int32_t sb_maha_debug_counters(sb_maha_t* h, int64_t* out8, uintptr_t stream);
 /* top-k eigenvectors of the last batch, d x k row-major (diagnostics / subspace parity tests) */
 int32_t sb_maha_get_eigvecs(sb_maha_t* h, double* h_V, uintptr_t stream);
@@ -191,6 +192,10 @@ int32_t sb_maha_get_eigvecs(sb_maha_t* h, double* h_V, uintptr_t stream);
 #define SB_OPT_PROFILE 3
 #define SB_OPT_FUSED_PASS2 4
 #define SB_OPT_LEGACY_MMA 5
+/* SB_OPT_NO_SUBSPACE 0|1: d = 128 / 256 take the top-k eigenvectors of every batch after the first from a warm-started
+ * block subspace iteration that accepts only under a proven spectral gap (csrc/maha_subspace.cu) and otherwise falls
+ * back to the Jacobi solver; 1 = always run the Jacobi solver */
+#define SB_OPT_NO_SUBSPACE 6
 int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t value);
 /* number of kernel launches issued through this handle so far (bench.py's gpu_launches) */
 int64_t sb_launch_count(void);

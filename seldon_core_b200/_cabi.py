@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(_HERE, "libsb200.so")
 
 SB_F32, SB_I32 = 0, 1
 SB_OPT_GRAM_TERMS, SB_OPT_FORCE_GENERIC, SB_OPT_PROFILE, SB_OPT_FUSED_PASS2, SB_OPT_LEGACY_MMA = 1, 2, 3, 4, 5
+SB_OPT_NO_SUBSPACE = 6
 SB_ROUTER_EPSILON_GREEDY, SB_ROUTER_THOMPSON = 0, 1
 SB_REWARD_PER_CALL, SB_REWARD_TABLE, SB_REWARD_BERNOULLI = 0, 1, 2
 SB_ROUTER_OPT_DEBUG_FALLBACK_PERIOD = 1

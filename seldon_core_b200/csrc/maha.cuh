@@ -68,6 +68,12 @@ int launch_pass1(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws,
 int launch_reduce(const sb_maha* h, const MahaWs& ws, double* stats_out, cudaStream_t st);
 int launch_finalize_cov(sb_maha* h, const double* all_stats, int nranks, int rank, const MahaWs& ws, cudaStream_t st);
 int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st);
+// warm-started block subspace iteration for the top-k eigenvectors (maha_subspace.cu)
+int subspace_block_doubles(int d);
+bool subspace_supported(int d, int KP);
+int launch_subspace_init(sb_maha* h, cudaStream_t st);
+int launch_subspace(sb_maha* h, int* conv_flag, cudaStream_t st);
+int launch_subspace_seed(sb_maha* h, const int* conv_flag, cudaStream_t st);
 int launch_prefix(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream_t st);
 int launch_score(sb_maha* h, const float* X, int64_t ld, float* score, int32_t* flag, const MahaWs& ws,
                  cudaStream_t st);
@@ -97,6 +103,9 @@ struct sb_maha {
   float *d_mean_f, *d_lo_f, *d_hi_f;       // fp32 copies of the committed state
   double *d_V, *d_PC0;                     // [d][KP], [KP][KP]
   double* d_Vfull;                         // [d][d] full Jacobi basis of the previous batch (warm start)
+  double* d_Vsub;                          // [d][32] block of the subspace iteration (d = 128 / 256), kept between batches
+  int sub_state;                           // 0: block not initialised, 1: guard vectors set, 2: holds a previous basis
+  int no_subspace;                         // SB_OPT_NO_SUBSPACE: always run the Jacobi solver
   int warm_batches;                        // batches since the last cold start of the eigensolver
   int no_cluster16;                        // a 16-CTA cluster launch failed once on this device: use 8
   const float *d_in_mu, *d_in_is;          // optional input transform (x - mu) * inv_sigma, caller-owned (sb_maha_set_input_transform)

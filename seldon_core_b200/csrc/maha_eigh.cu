@@ -448,7 +448,9 @@ template <int D, int NC>
 __global__ void __launch_bounds__(D * 16 / NC, 1)
 jacobi_cluster(const double* __restrict__ C, int k, int KP, double* __restrict__ gW, double* __restrict__ gV,
                double* __restrict__ Vd, float* __restrict__ Vf, double* __restrict__ evals,
-               long long* __restrict__ gate, double* __restrict__ Vfull, int warm, int* __restrict__ rot_flags) {
+               long long* __restrict__ gate, double* __restrict__ Vfull, int warm, int* __restrict__ rot_flags,
+               const int* __restrict__ skip) {
+  if (skip != nullptr && *skip != 0) return;  // the subspace iteration already delivered this batch's vectors
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   constexpr int SEATS = D / 2, SPC = SEATS / NC, PER = D / 32, CS = 2 * D;  // slot: W rows, then V rows
@@ -617,6 +619,26 @@ int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
     SB_CUDA(cudaFuncSetAttribute(jacobi64_regs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm64));
     jacobi64_regs<<<1, 512, sm64, st>>>(h->d_C1, h->k, h->KP, h->d_V, h->d_Vf, h->d_evals, h->d_gate, h->d_Vfull, warm);
   } else if ((d == 128 || d == 256) && !h->force_generic) {
+    // batches after the first: warm-started block subspace iteration on one CTA; the Jacobi solver below runs only
+    // when that reports no proven convergence (its `skip` word stays 0)
+    int* conv = reinterpret_cast<int*>(h->d_gate + 47);
+    const bool try_sub = h->d_Vsub != nullptr && !h->no_subspace && subspace_supported(d, h->KP);
+    const int* skip = nullptr;
+    if (try_sub) {
+      if (h->sub_state == 0) {
+        int rc = launch_subspace_init(h, st);
+        if (rc) return rc;
+        SB_CUDA(cudaMemsetAsync(h->d_gate + 46, 0, sizeof(long long), st));  // "block is orthonormal" word
+        h->sub_state = 1;
+      }
+      SB_CUDA(cudaMemsetAsync(conv, 0, sizeof(int), st));
+      SB_CUDA(cudaMemsetAsync(h->d_gate + 7, 0, sizeof(long long), st));
+      if (h->sub_state >= 2) {
+        int rc = launch_subspace(h, conv, st);
+        if (rc) return rc;
+        skip = conv;
+      }
+    }
     // cluster of 8 CTAs, columns in registers, neighbours exchange through (distributed) shared memory
     int* flags = reinterpret_cast<int*>(h->d_gate + 8);
     static const int nc = getenv("SB200_JACOBI_CLUSTER") ? atoi(getenv("SB200_JACOBI_CLUSTER")) : 16;
@@ -639,7 +661,7 @@ int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
       cfg.attrs = attr;
       cfg.numAttrs = 1;
       return cudaLaunchKernelEx(&cfg, kernel, (const double*)h->d_C1, h->k, h->KP, ws.eig_W, ws.eig_V, h->d_V, h->d_Vf,
-                                h->d_evals, h->d_gate, h->d_Vfull, warm, flags);
+                                h->d_evals, h->d_gate, h->d_Vfull, warm, flags, skip);
     };
     // 16 CTAs per cluster where the device schedules it (a full GPU does), else the portable 8
     cudaError_t ce = cudaErrorInvalidValue;
@@ -652,6 +674,11 @@ int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
     }
     if (ce != cudaSuccess) ce = d == 128 ? launch(jacobi_cluster<128, 8>, 8) : launch(jacobi_cluster<256, 8>, 8);
     SB_CUDA(ce);
+    if (try_sub) {
+      int rc = launch_subspace_seed(h, skip, st);  // a Jacobi result becomes the head of the block
+      if (rc) return rc;
+      h->sub_state = 2;
+    }
   } else if (need <= 200 * 1024) {
     SB_CUDA(cudaFuncSetAttribute(jacobi_topk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     jacobi_topk<true><<<1, 1024, need, st>>>(h->d_C1, d, h->k, h->KP, nullptr, nullptr, h->d_V, h->d_Vf, h->d_evals,

@@ -1051,10 +1051,14 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const float da = ra[q][e] - mm[e], db = rbv[q][e] - mm[e];
-          zb[0][e] = to_tf32(da);
-          zs[0][e] = to_tf32(da - __uint_as_float(zb[0][e]));
-          zb[1][e] = to_tf32(db);
-          zs[1][e] = to_tf32(db - __uint_as_float(zb[1][e]));
+          // TF32 split by truncation: the tensor core reads the top 19 bits of an operand register and ignores the
+          // rest, so the "hi" operand is the value itself (no instruction) and "lo" is what the truncation dropped
+          // (exact in fp32; itself truncated by the hardware: 2^-20 relative per product instead of 2^-22 with
+          // rounded parts, far inside the 1e-4 score tolerance)
+          zb[0][e] = __float_as_uint(da);
+          zs[0][e] = __float_as_uint(da - __uint_as_float(zb[0][e] & 0xffffe000u));
+          zb[1][e] = __float_as_uint(db);
+          zs[1][e] = __float_as_uint(db - __uint_as_float(zb[1][e] & 0xffffe000u));
         }
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
@@ -1088,9 +1092,11 @@ project_rows(const float* __restrict__ X, int64_t ld, SubLayout lay, const float
     for (int ks = 0; ks < 2; ++ks) {
       const float f0 = zt[(8 * ks + t) * 17 + g], f1 = zt[(8 * ks + t) * 17 + g + 8];
       const float f2 = zt[(8 * ks + t + 4) * 17 + g], f3 = zt[(8 * ks + t + 4) * 17 + g + 8];
-      const uint32_t b0 = to_tf32(f0), b1 = to_tf32(f1), b2 = to_tf32(f2), b3 = to_tf32(f3);
-      const uint32_t s0 = to_tf32(f0 - __uint_as_float(b0)), s1 = to_tf32(f1 - __uint_as_float(b1));
-      const uint32_t s2 = to_tf32(f2 - __uint_as_float(b2)), s3 = to_tf32(f3 - __uint_as_float(b3));
+      const uint32_t b0 = __float_as_uint(f0), b1 = __float_as_uint(f1), b2 = __float_as_uint(f2), b3 = __float_as_uint(f3);
+      const uint32_t s0 = __float_as_uint(f0 - __uint_as_float(b0 & 0xffffe000u));
+      const uint32_t s1 = __float_as_uint(f1 - __uint_as_float(b1 & 0xffffe000u));
+      const uint32_t s2 = __float_as_uint(f2 - __uint_as_float(b2 & 0xffffe000u));
+      const uint32_t s3 = __float_as_uint(f3 - __uint_as_float(b3 & 0xffffe000u));
       // n-tile 0 uses (k=t, n=g) = f0 and (k=t+4, n=g) = f2; n-tile 1 uses f1, f3
       mma_m16n8k8_tf32(qacc[0], s0, s1, s2, s3, b0, b2);
       mma_m16n8k8_tf32(qacc[0], b0, b1, b2, b3, s0, s2);

@@ -262,3 +262,51 @@ def test_fused_standardise_equals_the_two_step_graph(d):
     odd.fuse_standardise(StandardiseB200(mu[:18], sigma[:18]))
     with pytest.raises(SeldonB200Error):
         odd.score_device(torch.randn(500, 18, device=dev))
+
+
+def _counters(det):
+    import ctypes
+
+    import torch
+
+    out = (ctypes.c_int64 * 8)()
+    _cabi.check(_cabi.lib().sb_maha_debug_counters(det._h, out, torch.cuda.current_stream().cuda_stream))
+    return list(out)
+
+
+@pytest.mark.parametrize("d", [128, 256])
+def test_subspace_iteration_equals_the_jacobi_solver(d):
+    """d = 128 / 256, batches after the first: the top-k eigenvectors come from the warm-started block subspace
+    iteration (csrc/maha_subspace.cu).  On a spectrum with a gap it must be accepted and give the Jacobi solver's
+    projector, scores and flags; the oracle (scipy eigh) is the third witness."""
+    a, b, ref = (OutlierMahalanobisB200(n_components=16), OutlierMahalanobisB200(n_components=16),
+                 MahalanobisLean(n_components=16))
+    b.set_option(_cabi.SB_OPT_NO_SUBSPACE, 1)
+    for i, rows in enumerate((6000, 30001, 20000, 64, 9000)):
+        X, _ = synth.maha_rows_numpy(rows, d, 16, seed=700 + i)
+        pa, pb = a.predict(X, None), b.predict(X, None)
+        pr = ref.predict(X.astype(np.float64), None)
+        ca, cb = _counters(a), _counters(b)
+        assert cb[7] == 0
+        if i == 0:
+            assert ca[7] == 0                      # no previous basis yet: the Jacobi solver
+        else:
+            assert 1 <= ca[7] <= 8, "subspace iteration not accepted on a gapped spectrum: %d" % ca[7]
+        assert projector_err(a.eigvecs(), b.eigvecs()) < 3e-5   # acceptance bound of the iteration: 1e-5 * sqrt(2)
+        assert projector_err(a.eigvecs(), ref.V) < TOL
+        if i > 0:
+            assert rel_err(a.score, ref.score).max() < TOL and np.array_equal(pa, pr) and np.array_equal(pa, pb)
+
+
+def test_subspace_iteration_falls_back_without_a_gap():
+    """Isotropic data has no spectral gap at k: the iteration cannot prove that its block holds the dominant subspace,
+    reports failure, and the Jacobi solver runs - results equal to those of a handle with the iteration switched off."""
+    rs = np.random.RandomState(9)
+    a, b = OutlierMahalanobisB200(n_components=16), OutlierMahalanobisB200(n_components=16)
+    b.set_option(_cabi.SB_OPT_NO_SUBSPACE, 1)
+    for i in range(3):
+        X = rs.randn(20000, 128).astype(np.float32)
+        pa, pb = a.predict(X, None), b.predict(X, None)
+        if i > 0:
+            assert _counters(a)[7] < 0
+        assert np.array_equal(pa, pb) and rel_err(a.score, b.score).max() < 1e-5
