@@ -78,6 +78,17 @@ int32_t sb_json_ndarray_count(const uint8_t* d_text, uint64_t nbytes, void* d_ws
 int32_t sb_unpack_json_ndarray(const uint8_t* d_text, uint64_t nbytes, int64_t rows, int64_t cols, const void* d_ws,
                                float* d_out, int64_t ld, int32_t* d_status, uintptr_t stream);
 
+/* REST JSON, encode direction: the text json.dumps writes for a rows x cols matrix (cols == 0: a flat list of `rows`
+ * values) of in_dtype SB_F32 (every value widened to binary64 and written as float.__repr__ writes it: the shortest
+ * decimal that reads back as the same double) or SB_I32 (ints).  Replaces the `.tolist()` + json.dumps of the response
+ * path, python/seldon_core/utils.py:345-384 (construct_response_json: "ndarray": array.tolist() /
+ * "tensor": {"values": array.ravel().tolist()}).  d_text must hold sb_json_text_capacity(rows, cols) bytes; the number of
+ * bytes written goes to *d_nbytes (device); d_ws: sb_json_encode_workspace_bytes(rows, cols) bytes, 8-byte aligned. */
+uint64_t sb_json_text_capacity(int64_t rows, int64_t cols);
+uint64_t sb_json_encode_workspace_bytes(int64_t rows, int64_t cols);
+int32_t sb_pack_json_ndarray(const void* d_in, int32_t in_dtype, int64_t rows, int64_t cols, void* d_ws, uint64_t ws_bytes,
+                             uint8_t* d_text, uint64_t* d_nbytes, uintptr_t stream);
+
 /* --------------------------------------------------------------------------------------------- combiner
  * replaces examples/combiners/mnist_combiner/MnistCombiner.py:8-11 and the N-child rule of
  * engine/src/main/java/io/seldon/engine/predictors/AverageCombinerUnit.java:35-79: out = (sum_j in_j) / N,

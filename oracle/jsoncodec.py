@@ -69,3 +69,112 @@ def eisel_lemire(q, w):
         mant &= ~(1 << 52)
         bits = (0x7ff << 52) if power2 >= 0x7ff else ((power2 << 52) | mant)
     return struct.unpack("<d", struct.pack("<Q", bits))[0]
+
+
+# ------------------------------------------------------------------------------------------------ encode direction
+# Reference path: python/seldon_core/utils.py:306-407 (`construct_response_json`): the result array goes through
+# `.tolist()` and the wrapper's `json.dumps`, i.e. every float is written by CPython's float.__repr__ (the shortest
+# decimal string that reads back as the same binary64, the closest one when there are several) and every int as an int.
+# `encode()` IS that path.  `shortest_decimal()` / `format_repr()` restate csrc/jsonencode.cu (Schubfach with the
+# tabulated powers of ten of tools/gen_pow10_table.py, then CPython's repr layout rules, Python/pystrtod.c
+# format_float_short with mode 'r': exponent form iff decpt <= -4 or decpt > 16); the CPU tests check them against
+# repr() so that a wrong table or rounding rule is caught without a GPU.
+
+def encode(arr):
+    """The text json.dumps writes for the "ndarray" member of a response."""
+    return json.dumps(np.asarray(arr).tolist()).encode()
+
+
+_G = None
+_M63 = (1 << 63) - 1
+
+
+def _g(k):
+    global _G
+    if _G is None:
+        from gen_pow10_table import K_MIN, table as t10
+
+        _G = (K_MIN, t10())
+    return _G[1][k - _G[0]]
+
+
+def _rop(g1, g0, cp):
+    x1 = (g0 * cp) >> 64
+    y0 = (g1 * cp) & _M64
+    y1 = (g1 * cp) >> 64
+    z = (y0 >> 1) + x1
+    vbp = y1 + (z >> 63)
+    return vbp | (((z & _M63) + _M63) >> 63)
+
+
+def shortest_decimal(bits):
+    """(digits, exponent) with value = digits * 10**exponent, digits without trailing zeros, for a finite positive
+    binary64 given by its bit pattern."""
+    t = bits & ((1 << 52) - 1)
+    bq = (bits >> 52) & 0x7FF
+    if bq:
+        c, q = t | (1 << 52), bq - 1075
+    else:
+        c, q = t, -1074
+    out = c & 1
+    cb = c << 2
+    cbr = cb + 2
+    if c != (1 << 52) or q == -1074:
+        cbl = cb - 2
+        k = (q * 661971961083) >> 41
+    else:
+        cbl = cb - 1
+        k = (q * 661971961083 - 274743187321) >> 41
+    h = q + ((-k * 913124641741) >> 38) + 2
+    g1, g0 = _g(-k)
+    vb = _rop(g1, g0, cb << h)
+    vbl = _rop(g1, g0, cbl << h)
+    vbr = _rop(g1, g0, cbr << h)
+    lower, upper = vbl + out, vbr - out
+    s = vb >> 2
+    done = False
+    if s >= 10:
+        sp = s // 10
+        up_in = lower <= 40 * sp
+        wp_in = 40 * sp + 40 <= upper
+        if up_in != wp_in:
+            dig, e = sp + int(wp_in), k + 1
+            done = True
+    if not done:
+        u_in = lower <= 4 * s
+        w_in = 4 * s + 4 <= upper
+        if u_in != w_in:
+            dig, e = s + int(w_in), k
+        else:
+            mid = 4 * s + 2
+            dig, e = s + int(vb > mid or (vb == mid and (s & 1))), k
+    while dig % 10 == 0:
+        dig //= 10
+        e += 1
+    return dig, e
+
+
+def format_repr(x):
+    """float.__repr__ from shortest_decimal (json.dumps spellings for the non-finite values)."""
+    if x != x:
+        return "NaN"
+    if x in (float("inf"), float("-inf")):
+        return "Infinity" if x > 0 else "-Infinity"
+    bits = struct.unpack("<Q", struct.pack("<d", x))[0]
+    sign = "-" if bits >> 63 else ""
+    bits &= (1 << 63) - 1
+    if bits == 0:
+        return sign + "0.0"
+    dig, e = shortest_decimal(bits)
+    ds = str(dig)
+    nd = len(ds)
+    decpt = nd + e
+    if decpt <= -4 or decpt > 16:
+        ex = decpt - 1
+        mant = ds[0] + ("." + ds[1:] if nd > 1 else "")
+        return "%s%se%s%02d" % (sign, mant, "-" if ex < 0 else "+", abs(ex))
+    if decpt <= 0:
+        return sign + "0." + "0" * (-decpt) + ds
+    if decpt >= nd:
+        return sign + ds + "0" * (decpt - nd) + ".0"
+    return sign + ds[:decpt] + "." + ds[decpt:]

@@ -36,6 +36,9 @@ SIGNATURES = {
     "sb_json_ndarray_count": (c_int32, [c_void_p, c_uint64, c_void_p, c_uint64, c_void_p, _uintptr]),
     "sb_unpack_json_ndarray": (c_int32, [c_void_p, c_uint64, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p,
                                          _uintptr]),
+    "sb_json_text_capacity": (c_uint64, [c_int64, c_int64]),
+    "sb_json_encode_workspace_bytes": (c_uint64, [c_int64, c_int64]),
+    "sb_pack_json_ndarray": (c_int32, [c_void_p, c_int32, c_int64, c_int64, c_void_p, c_uint64, c_void_p, c_void_p, _uintptr]),
     "sb_feedback_state_bytes": (c_uint64, [c_int32]),
     "sb_feedback_reset": (c_int32, [c_void_p, c_int32, _uintptr]),
     "sb_feedback_update": (c_int32, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, _uintptr]),

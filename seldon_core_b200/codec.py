@@ -213,15 +213,17 @@ def class_names(result_ndim, n_targets, user_names=None):
 
 # ---------------------------------------------------------------------------------------------- REST JSON
 _NDARRAY_KEY = re.compile(rb'"ndarray"\s*:\s*\[')
+_VALUES_KEY = re.compile(rb'"values"\s*:\s*\[')
 _END_2D = re.compile(rb'\]\s*\]')
 
 
-def json_ndarray_span(payload):
-    """(start, end, ndim) of the value of "ndarray" in a REST request body (`{"data": {"ndarray": [[..], ..]}}`,
-    utils.py:499-505), found without parsing the numbers: start at its opening bracket, end one past its closing one."""
-    m = _NDARRAY_KEY.search(payload)
+def json_ndarray_span(payload, key="ndarray"):
+    """(start, end, ndim) of the value of "ndarray" (or of the tensor's "values") in a REST request body
+    (`{"data": {"ndarray": [[..], ..]}}`, utils.py:499-505), found without parsing the numbers: start at its opening
+    bracket, end one past its closing one."""
+    m = (_NDARRAY_KEY if key == "ndarray" else _VALUES_KEY).search(payload)
     if m is None:
-        raise SeldonB200Error('no "ndarray" member in the payload')
+        raise SeldonB200Error('no "%s" member in the payload' % key)
     start = m.end() - 1
     i = start + 1
     while i < len(payload) and payload[i:i + 1] in (b" ", b"\n", b"\r", b"\t"):
@@ -237,8 +239,9 @@ def json_ndarray_span(payload):
     return start, e + 1, 1
 
 
-def decode_json_ndarray(payload, device=None):
-    """REST JSON body (bytes) -> CUDA float32 array holding data.ndarray, shape (rows, cols) or (n,) for a flat list.
+def decode_json_ndarray(payload, device=None, key="ndarray"):
+    """REST JSON body (bytes) -> CUDA float32 array holding data.ndarray (or, with key="values", the flat values of
+    data.tensor), shape (rows, cols) or (n,) for a flat list.
 
     Replaces `json.loads` + `np.array(datadef["ndarray"])` (utils.py:499-505): every number gets the correctly rounded
     binary64 value CPython's float() gives it, narrowed to fp32.  Non-numeric or ragged arrays raise."""
@@ -246,7 +249,7 @@ def decode_json_ndarray(payload, device=None):
 
     if isinstance(payload, str):
         payload = payload.encode("utf-8")
-    start, end, ndim = json_ndarray_span(payload)
+    start, end, ndim = json_ndarray_span(payload, key)
     text = payload[start:end]
     dev = _device(device)
     L = _cabi.lib()
@@ -277,3 +280,35 @@ def decode_json_ndarray(payload, device=None):
     if st != 0:
         raise SeldonB200Error('"ndarray" is not a rectangular array of JSON numbers')
     return out.view(-1) if ndim == 1 else out
+
+
+def encode_json_ndarray_device(t):
+    """CUDA float32 / int32 tensor (1-D or 2-D) -> (CUDA uint8 tensor holding the text json.dumps(t.tolist()) writes,
+    its length as a CUDA int64 scalar).  No host synchronisation."""
+    import torch
+
+    t = t.contiguous()
+    if t.dim() == 1:
+        rows, cols = t.shape[0], 0
+    elif t.dim() == 2:
+        rows, cols = t.shape
+        if rows and not cols:
+            raise SeldonB200Error("rows of zero columns are not supported")
+    else:
+        raise SeldonB200Error("encode_json_ndarray supports 1-D and 2-D tensors")
+    L = _cabi.lib()
+    text = torch.empty(int(L.sb_json_text_capacity(rows, cols)), dtype=torch.uint8, device=t.device)
+    ws = torch.empty((int(L.sb_json_encode_workspace_bytes(rows, cols)) + 7) // 8, dtype=torch.int64, device=t.device)
+    nbytes = torch.zeros(1, dtype=torch.int64, device=t.device)
+    with torch.cuda.device(t.device):
+        _cabi.check(L.sb_pack_json_ndarray(t.data_ptr(), _dtype_code(t), rows, cols, ws.data_ptr(), ws.numel() * 8,
+                                           text.data_ptr(), nbytes.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    return text, nbytes
+
+
+def encode_json_ndarray(t):
+    """CUDA float32 / int32 tensor -> bytes: the value of "ndarray" (or of tensor "values" for a flat tensor) exactly
+    as `json.dumps(array.tolist())` of the reference's response path writes it (utils.py:345-384)."""
+    text, nbytes = encode_json_ndarray_device(t)
+    n = int(nbytes.item())
+    return text[:n].cpu().numpy().tobytes()

@@ -96,6 +96,8 @@ class OutlierMahalanobisB200(object):
 
         if isinstance(msg, dict):
             return self._raw_json(msg, transform)
+        if isinstance(msg, (bytes, bytearray, str)) and msg[:1] in (b"{", "{"):
+            return self._raw_rest_text(msg, transform)
         with self._lock:
             if self._wire is None:
                 self._wire = wire.WireStage(self._pick_device())
@@ -119,6 +121,69 @@ class OutlierMahalanobisB200(object):
         if hasattr(msg, "SerializeToString"):
             return type(msg).FromString(resp.tobytes())
         return resp
+
+    def _raw_rest_text(self, body, transform):
+        """REST: the body as TEXT (bytes), before any json.loads - `{"data": {"names": [...], "ndarray": [[...]]}}` or
+        `{"data": {"tensor": {"shape": [...], "values": [...]}}}` (utils.py:472-525).  The numbers are converted on the
+        device in both directions (decimal text -> binary64 -> fp32, csrc/jsoncodec.cu; flags -> text,
+        csrc/jsonencode.cu); only the rest of the body - names, meta - goes through the json module.  Returns the
+        response body as bytes, laid out as json.dumps of construct_response_json's dict (utils.py:306-407).  In
+        transformer mode the request's array text is echoed as it was sent (the reference re-serialises the same
+        numbers)."""
+        import json
+
+        import torch
+
+        from . import codec
+
+        if isinstance(body, str):
+            body = body.encode("utf-8")
+        body = bytes(body)
+        with self._lock:
+            dev = self._pick_device()
+            kind = "tensor" if codec._VALUES_KEY.search(body) and b'"tensor"' in body else "ndarray"
+            key = "values" if kind == "tensor" else "ndarray"
+            start, end, ndim = codec.json_ndarray_span(body, key)
+            rest = json.loads(body[:start] + b"null" + body[end:])
+            d = rest.get("data") or {}
+            X = codec.decode_json_ndarray(body, dev, key)
+            if kind == "tensor":
+                shape = [int(v) for v in d["tensor"]["shape"]]
+                if len(shape) != 2 or shape[0] * shape[1] != X.numel():
+                    raise SeldonB200Error("tensor payload: shape %s does not match %d values" % (shape, X.numel()))
+                X = X.view(shape[0], shape[1])
+            if X.dim() != 2:
+                raise SeldonB200Error("expected a 2-D batch, got shape %s" % (tuple(X.shape),))
+            _, flag = self.score_device(X.contiguous())
+            holes = {}
+
+            def hole(text):
+                k = "@@sb200:%d@@" % len(holes)
+                holes[k] = text
+                return k
+
+            if transform:
+                self.prediction_meta = flag.cpu().numpy().astype(int)
+                arr = hole(body[start:end])
+                names = d.get("names", [])
+            else:
+                arr = hole(codec.encode_json_ndarray(flag))
+                names = []
+            data = {kind: {"values": arr, "shape": list(d["tensor"]["shape"]) if transform else [int(flag.numel())]}
+                    if kind == "tensor" else arr, "names": names}
+            resp = {"data": data, "meta": {}}
+            if transform:
+                resp["meta"]["tags"] = {"outlier-predictions": hole(codec.encode_json_ndarray(flag))}
+            elif self.tags():
+                resp["meta"]["tags"] = self.tags()
+            resp["meta"]["metrics"] = self.metrics()
+            puid = (rest.get("meta") or {}).get("puid")
+            if puid:
+                resp["meta"]["puid"] = puid
+            out = json.dumps(resp).encode("utf-8")
+            for k, text in holes.items():
+                out = out.replace(b'"' + k.encode() + b'"', text, 1)
+            return out
 
     def _raw_json(self, request, transform):
         """REST: the body has already been parsed by json.loads (seldon_methods.py:53-57 -> construct_response_json,

@@ -78,3 +78,75 @@ def test_chunk_boundaries_large():
     p = body(a.tolist())
     assert len(p) > 100 * 4096
     assert np.array_equal(codec.decode_json_ndarray(p).cpu().numpy(), ref_decode(p))
+
+
+def _corpus(n, seed):
+    """doubles that are exactly representable in fp32, spread over magnitudes, with the layout edge cases of repr()."""
+    rs = np.random.RandomState(seed)
+    a = (rs.randn(n) * 10.0 ** rs.randint(-12, 13, size=n)).astype(np.float32)
+    special = np.array([0.0, -0.0, 1.0, -1.0, 0.1, 0.5, 1e16, 1e15, 9999999827968.0, 1e22, 1e-5, 1e-4, 123456.789, 16777216.0,
+                        3.4028234663852886e38, 1.401298464324817e-45, 1.1754943508222875e-38, 1e-7, 100.0, 2.5e-5,
+                        np.inf, -np.inf, np.nan, 0.30000001192092896, 1e21, 123456792.0], dtype=np.float32)
+    a[:len(special)] = special
+    return a
+
+
+@pytest.mark.parametrize("shape", [(1,), (7,), (1, 1), (3, 4), (1000, 17), (4096, 64), (1, 5000)])
+def test_encode_json_text_equals_json_dumps(shape):
+    """SURVEY 8(f) row 1, encode direction: the device text is byte for byte what json.dumps(array.tolist()) writes
+    (utils.py:345-384), for floats (shortest repr) and ints."""
+    import torch
+
+    n = int(np.prod(shape))
+    a = _corpus(max(n, 32), 7)[:n].reshape(shape)
+    got = codec.encode_json_ndarray(torch.from_numpy(a).cuda())
+    with np.errstate(all="ignore"):
+        want = json.dumps(a.astype(np.float64).tolist()).encode()
+    assert got == want
+    ints = np.random.RandomState(1).randint(-2 ** 31, 2 ** 31 - 1, size=shape).astype(np.int32)
+    ints.flat[0] = -2 ** 31
+    assert codec.encode_json_ndarray(torch.from_numpy(ints).cuda()) == json.dumps(ints.tolist()).encode()
+    assert codec.encode_json_ndarray(torch.empty(0, dtype=torch.float32, device="cuda")) == b"[]"
+
+
+def test_encode_json_corpus_500k_and_round_trip():
+    """500 k values (the size of the decode table's check corpus): every number's text equals repr(), and decoding the
+    text on the device gives the values back bit for bit."""
+    import torch
+
+    a = _corpus(500000, 11)
+    a = a[np.isfinite(a)]
+    a = a[:len(a) // 4 * 4].reshape(-1, 4)
+    t = torch.from_numpy(a).cuda()
+    text = codec.encode_json_ndarray(t)
+    assert text == json.dumps(a.astype(np.float64).tolist()).encode()
+    back = codec.decode_json_ndarray(b'{"data":{"ndarray":' + text + b'}}')
+    assert torch.equal(back.view(torch.int32), t.view(torch.int32))
+
+
+def test_predict_raw_on_rest_text():
+    """The REST body as text through predict_raw / transform_input_raw: numbers decoded and encoded on the device; the
+    response parses to what construct_response_json builds from the oracle's flags."""
+    from oracle.mahalanobis import MahalanobisLean
+    from seldon_core_b200 import OutlierMahalanobisB200, synth
+
+    prime, _ = synth.maha_rows_numpy(3000, 18, 4, seed=83)
+    X, _ = synth.maha_rows_numpy(400, 18, 4, seed=84)
+    det, ref = OutlierMahalanobisB200(n_components=4), MahalanobisLean(n_components=4)
+    det.predict(prime, None), ref.predict(prime.astype(np.float64), None)
+    names = ["c%d" % i for i in range(18)]
+    body = json.dumps({"meta": {"puid": "r1"}, "data": {"names": names, "ndarray": X.astype(np.float64).tolist()}}).encode()
+    out = det.predict_raw(body)
+    want = ref.predict(X.astype(np.float64), names)
+    resp = json.loads(out)
+    assert resp["data"] == {"ndarray": want.tolist(), "names": []} and resp["meta"]["puid"] == "r1"
+    assert [m["key"] for m in resp["meta"]["metrics"]] == [m["key"] for m in ref.metrics()]
+    assert b'"ndarray": ' + json.dumps(want.tolist()).encode() in out        # the device text, spliced in as it is
+    X2, _ = synth.maha_rows_numpy(77, 18, 4, seed=85)
+    body = json.dumps({"data": {"tensor": {"shape": [77, 18], "values": X2.astype(np.float64).ravel().tolist()}}}).encode()
+    out = det.transform_input_raw(body)
+    want2 = ref.predict(X2.astype(np.float64), None)
+    resp = json.loads(out)
+    assert resp["data"]["tensor"]["shape"] == [77, 18]
+    assert resp["data"]["tensor"]["values"] == X2.astype(np.float64).ravel().tolist()
+    assert resp["meta"]["tags"] == {"outlier-predictions": want2.tolist()}
