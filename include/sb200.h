@@ -232,6 +232,11 @@ int32_t sb_router_run(sb_router_t* h, int64_t T, const int64_t* d_rows_per_call,
 /* route() of the class API (EpsilonGreedy.py:87-106, ThompsonSampling.py:78-91): one decision, written by the kernel
  * into pinned host memory owned by the handle and returned in *h_out.  Synchronises the stream. */
 int32_t sb_router_route(sb_router_t* h, int32_t* h_out, uintptr_t stream);
+/* send_feedback(routing = arm, rows, reward) of the previous request followed by the next route(), in ONE launch: the
+ * request loop of the wrapper (seldon_methods.py:59-103 then L196-243) costs one launch and one synchronisation per
+ * request instead of two launches.  Same decisions as sb_router_feedback + sb_router_route. */
+int32_t sb_router_feedback_route(sb_router_t* h, int32_t arm, int64_t rows, double reward, int32_t* h_out,
+                                 uintptr_t stream);
 /* Thompson: the n beta samples of the last route (self.branch_values, ThompsonSampling.py:81-82).  Synchronises. */
 int32_t sb_router_last_values(sb_router_t* h, double* h_values, uintptr_t stream);
 /* single feedback for an externally chosen arm (send_feedback of the class API) */

@@ -69,6 +69,7 @@ SIGNATURES = {
     "sb_router_get_state": (c_int32, [c_void_p, c_void_p, _uintptr]),
     "sb_router_set_state": (c_int32, [c_void_p, c_void_p, _uintptr]),
     "sb_router_route": (c_int32, [c_void_p, POINTER(c_int32), _uintptr]),
+    "sb_router_feedback_route": (c_int32, [c_void_p, c_int32, c_int64, c_double, POINTER(c_int32), _uintptr]),
     "sb_router_last_values": (c_int32, [c_void_p, c_void_p, _uintptr]),
     "sb_abtest_initial_state": (c_uint64, [c_int64]),
     "sb_abtest_route": (c_int32, [c_void_p, ctypes.c_float, c_int64, c_void_p, _uintptr]),

@@ -35,6 +35,8 @@ def build_library(force=False, verbose=False):
         objs.append(obj)
         if force or _stale(obj, [src] + hdrs):
             extra = ["-fmad=false"] if os.path.basename(src) == "routers.cu" else []  # bit-exact fp64 vs the C streams
+            if os.environ.get("SB_NVTX"):
+                extra.append("-DSB_NVTX")  # NVTX ranges around every sb_* entry point (common.cuh)
             cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
             jobs.append(cmd)
 
@@ -50,7 +52,7 @@ def build_library(force=False, verbose=False):
         for l in logs:
             sys.stderr.write(l)
     if force or jobs or _stale(LIB, objs):
-        run([nvcc, "-shared", "-o", LIB] + objs + ["-lcudart"])
+        run([nvcc, "-shared", "-o", LIB] + objs + ["-lcudart"] + (["-ldl"] if os.environ.get("SB_NVTX") else []))
     return LIB
 
 

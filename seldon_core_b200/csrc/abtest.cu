@@ -53,6 +53,7 @@ abtest_route_kernel(unsigned long long* __restrict__ state, float ratio_a, long 
 extern "C" uint64_t sb_abtest_initial_state(int64_t seed) { return ((uint64_t)seed ^ kMul) & kMask; }
 
 extern "C" int32_t sb_abtest_route(uint64_t* d_state2, float ratio_a, int64_t T, int32_t* d_decisions, uintptr_t stream) {
+  SB_RANGE("sb_abtest_route");
   SB_REQUIRE(d_state2 && T >= 0, SB_ERR_INVALID, "sb_abtest_route: bad arguments");
   SB_REQUIRE(ratio_a == ratio_a, SB_ERR_INVALID, "Parameter 'ratioA' is missing.");
   if (T == 0) return SB_OK;

@@ -19,5 +19,6 @@ void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 }  // namespace sb
 
 extern "C" const char* sb_last_error(void) { return sb::g_err; }
-extern "C" int32_t sb_version(void) { return 100; }
+extern "C" int32_t sb_version(void) {
+  SB_RANGE("sb_version"); return 100; }
 extern "C" int64_t sb_launch_count(void) { return sb::g_launches.load(std::memory_order_relaxed); }

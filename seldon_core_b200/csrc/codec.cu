@@ -663,6 +663,7 @@ extern "C" int32_t sb_unpack_tensor_f64(const uint8_t* d_wire, uint64_t wire_nby
                                         int64_t cols,
                                         const float* d_mu, const float* d_inv_sigma, float* d_out, int64_t ld,
                                         uintptr_t stream) {
+  SB_RANGE("sb_unpack_tensor_f64");
   SB_REQUIRE(rows >= 0 && cols >= 1 && ld >= cols, SB_ERR_INVALID, "sb_unpack_tensor_f64: bad shape");
   SB_REQUIRE((d_mu == nullptr) == (d_inv_sigma == nullptr), SB_ERR_INVALID, "sb_unpack_tensor_f64: mu and inv_sigma go together");
   SB_REQUIRE(values_off <= wire_nbytes && (uint64_t)rows <= (wire_nbytes - values_off) / 8 / (uint64_t)cols, SB_ERR_INVALID,
@@ -699,6 +700,7 @@ extern "C" int32_t sb_unpack_tensor_f64(const uint8_t* d_wire, uint64_t wire_nby
 
 extern "C" int32_t sb_unpack_listvalue(const uint8_t* d_wire, uint64_t nbytes, int64_t rows, int64_t cols, float* d_out,
                                        int64_t ld, int32_t* d_status, uintptr_t stream) {
+  SB_RANGE("sb_unpack_listvalue");
   SB_REQUIRE(rows >= 0 && cols >= 1 && ld >= cols, SB_ERR_INVALID, "sb_unpack_listvalue: bad shape");
   SB_REQUIRE(d_status != nullptr, SB_ERR_INVALID, "sb_unpack_listvalue: status word required");
   SB_REQUIRE(nbytes == sb_listvalue_nbytes(rows, cols), SB_ERR_INVALID,
@@ -745,6 +747,7 @@ extern "C" int32_t sb_unpack_listvalue(const uint8_t* d_wire, uint64_t nbytes, i
 
 extern "C" int32_t sb_pack_tensor_f64(const void* d_in, int32_t in_dtype, int64_t n, uint8_t* d_wire_values,
                                       uintptr_t stream) {
+  SB_RANGE("sb_pack_tensor_f64");
   SB_REQUIRE(n >= 0 && (in_dtype == SB_F32 || in_dtype == SB_I32), SB_ERR_INVALID, "sb_pack_tensor_f64: bad arguments");
   if (n == 0) return SB_OK;
   SB_REQUIRE(d_in && d_wire_values, SB_ERR_INVALID, "sb_pack_tensor_f64: null buffer");
@@ -769,6 +772,7 @@ extern "C" int32_t sb_pack_tensor_f64(const void* d_in, int32_t in_dtype, int64_
 
 extern "C" int32_t sb_pack_listvalue(const void* d_in, int32_t in_dtype, int64_t rows, int64_t cols, uint8_t* d_wire,
                                      uintptr_t stream) {
+  SB_RANGE("sb_pack_listvalue");
   SB_REQUIRE(rows >= 0 && cols >= 0 && (in_dtype == SB_F32 || in_dtype == SB_I32), SB_ERR_INVALID,
              "sb_pack_listvalue: bad arguments");
   if (rows == 0) return SB_OK;

@@ -115,6 +115,7 @@ __global__ void __launch_bounds__(256) standardise_vec4(const float4* __restrict
 
 extern "C" int32_t sb_combiner_mean(const float* const* h_inputs, int32_t n_children, int64_t n_elems, float* d_out,
                                     uintptr_t stream) {
+  SB_RANGE("sb_combiner_mean");
   SB_REQUIRE(h_inputs != nullptr && n_children >= 1, SB_ERR_INVALID, "Combiner received no inputs");
   SB_REQUIRE(n_children <= kMaxChildren, SB_ERR_INVALID, "sb_combiner_mean: at most %d children", kMaxChildren);
   SB_REQUIRE(n_elems >= 0 && (d_out != nullptr || n_elems == 0), SB_ERR_INVALID, "sb_combiner_mean: bad output");
@@ -153,6 +154,7 @@ extern "C" int32_t sb_combiner_mean(const float* const* h_inputs, int32_t n_chil
 
 extern "C" int32_t sb_standardise(const float* d_in, int64_t rows, int64_t cols, int64_t ld_in, const float* d_mu,
                                   const float* d_inv_sigma, float* d_out, int64_t ld_out, uintptr_t stream) {
+  SB_RANGE("sb_standardise");
   SB_REQUIRE(rows >= 0 && cols >= 1 && ld_in >= cols && ld_out >= cols, SB_ERR_INVALID, "sb_standardise: bad shape");
   SB_REQUIRE(d_mu && d_inv_sigma, SB_ERR_INVALID, "sb_standardise: mu/inv_sigma required");
   if (rows == 0) return SB_OK;

@@ -35,6 +35,20 @@ void count_launch(int n = 1);
     SB_CUDA(cudaGetLastError());                                                                   \
   } while (0)
 
+// NVTX ranges around the C-ABI entry points: compiled in with -DSB_NVTX (build.py: environment SB_NVTX=1), absent otherwise
+#ifdef SB_NVTX
+}  // namespace sb
+#include <nvtx3/nvToolsExt.h>
+namespace sb {
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
+#define SB_RANGE(name) sb::NvtxRange sb_nvtx_range__(name)
+#else
+#define SB_RANGE(name) do { } while (0)
+#endif
+
 constexpr int kNumSMs = 148;  // B200
 
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }

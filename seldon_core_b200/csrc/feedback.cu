@@ -117,6 +117,7 @@ extern "C" uint64_t sb_feedback_state_bytes(int32_t roll_window) {
 }
 
 extern "C" int32_t sb_feedback_reset(void* d_state, int32_t roll_window, uintptr_t stream) {
+  SB_RANGE("sb_feedback_reset");
   SB_REQUIRE(d_state && roll_window >= 1, SB_ERR_INVALID, "sb_feedback_reset: bad arguments");
   SB_REQUIRE(((uintptr_t)d_state & 7) == 0, SB_ERR_INVALID, "sb_feedback_reset: state must be 8-byte aligned");
   const int64_t words = (int64_t)(sb_feedback_state_bytes(roll_window) / 8);
@@ -127,6 +128,7 @@ extern "C" int32_t sb_feedback_reset(void* d_state, int32_t roll_window, uintptr
 
 extern "C" int32_t sb_feedback_update(const int32_t* d_pred, const int32_t* d_truth, int64_t n, void* d_state,
                                       double* d_metrics18, uintptr_t stream) {
+  SB_RANGE("sb_feedback_update");
   SB_REQUIRE(n >= 0 && d_state && d_metrics18, SB_ERR_INVALID, "sb_feedback_update: bad arguments");
   SB_REQUIRE(n == 0 || (d_pred && d_truth), SB_ERR_INVALID, "sb_feedback_update: null flags");
   cudaStream_t st = (cudaStream_t)stream;

@@ -330,6 +330,7 @@ extern "C" uint64_t sb_json_workspace_bytes(uint64_t nbytes) {
 
 extern "C" int32_t sb_json_ndarray_count(const uint8_t* d_text, uint64_t nbytes, void* d_ws, uint64_t ws_bytes,
                                          int64_t* d_counts4, uintptr_t stream) {
+  SB_RANGE("sb_json_ndarray_count");
   SB_REQUIRE(d_text && nbytes >= 2 && d_ws && d_counts4, SB_ERR_INVALID, "sb_json_ndarray_count: bad arguments");
   SB_REQUIRE(((uintptr_t)d_ws & 7) == 0 && ws_bytes >= sb_json_workspace_bytes(nbytes), SB_ERR_WORKSPACE,
              "sb_json_ndarray_count: workspace too small or misaligned");
@@ -347,6 +348,7 @@ extern "C" int32_t sb_json_ndarray_count(const uint8_t* d_text, uint64_t nbytes,
 extern "C" int32_t sb_unpack_json_ndarray(const uint8_t* d_text, uint64_t nbytes, int64_t rows, int64_t cols,
                                           const void* d_ws, float* d_out, int64_t ld, int32_t* d_status,
                                           uintptr_t stream) {
+  SB_RANGE("sb_unpack_json_ndarray");
   SB_REQUIRE(d_text && nbytes >= 2 && d_ws && d_status, SB_ERR_INVALID, "sb_unpack_json_ndarray: bad arguments");
   SB_REQUIRE(rows >= 0 && cols >= 0 && ld >= cols, SB_ERR_INVALID, "sb_unpack_json_ndarray: bad shape");
   SB_REQUIRE(rows * cols == 0 || d_out, SB_ERR_INVALID, "sb_unpack_json_ndarray: null output");

@@ -95,6 +95,7 @@ using namespace sb;
 
 extern "C" int32_t sb_maha_create(sb_maha_t** out, int32_t d, int32_t n_components, double threshold, double n_stdev,
                                   int64_t start_clip, int64_t max_n) {
+  SB_RANGE("sb_maha_create");
   SB_REQUIRE(out != nullptr, SB_ERR_INVALID, "sb_maha_create: null handle pointer");
   SB_REQUIRE(d >= 1 && d <= kMaxD, SB_ERR_INVALID, "sb_maha_create: d=%d outside 1..%d", d, kMaxD);
   SB_REQUIRE(n_components >= 1, SB_ERR_INVALID, "sb_maha_create: n_components must be >= 1");
@@ -135,6 +136,7 @@ extern "C" int32_t sb_maha_create(sb_maha_t** out, int32_t d, int32_t n_componen
 }
 
 extern "C" int32_t sb_maha_destroy(sb_maha_t* h) {
+  SB_RANGE("sb_maha_destroy");
   if (!h) return SB_OK;
   if (h->profile)
     for (int i = 0; i < 10; ++i) cudaEventDestroy(h->ev[i]);
@@ -146,6 +148,7 @@ extern "C" int32_t sb_maha_destroy(sb_maha_t* h) {
 }
 
 extern "C" int32_t sb_maha_workspace_bytes(const sb_maha_t* h, int64_t max_rows, uint64_t* bytes) {
+  SB_RANGE("sb_maha_workspace_bytes");
   SB_REQUIRE(h && bytes && max_rows >= 1, SB_ERR_INVALID, "sb_maha_workspace_bytes: bad arguments");
   *bytes = carve(h, max_subsegments(max_rows), max_subsegments2(max_rows), max_rows, nullptr, nullptr);
   return SB_OK;
@@ -154,6 +157,7 @@ extern "C" int32_t sb_maha_workspace_bytes(const sb_maha_t* h, int64_t max_rows,
 extern "C" int64_t sb_maha_stats_len(const sb_maha_t* h) { return h ? 1 + (int64_t)h->d + (int64_t)h->d * h->d : 0; }
 
 extern "C" int32_t sb_maha_set_input_transform(sb_maha_t* h, const float* d_mu, const float* d_inv_sigma) {
+  SB_RANGE("sb_maha_set_input_transform");
   SB_REQUIRE(h, SB_ERR_INVALID, "sb_maha_set_input_transform: null handle");
   SB_REQUIRE((d_mu == nullptr) == (d_inv_sigma == nullptr), SB_ERR_INVALID,
              "sb_maha_set_input_transform: mu and inv_sigma go together");
@@ -166,6 +170,7 @@ extern "C" int32_t sb_maha_set_input_transform(sb_maha_t* h, const float* d_mu, 
 }
 
 extern "C" int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t value) {
+  SB_RANGE("sb_maha_set_option");
   SB_REQUIRE(h, SB_ERR_INVALID, "sb_maha_set_option: null handle");
   if (option == SB_OPT_GRAM_TERMS) {
     SB_REQUIRE(value == 1 || value == 3, SB_ERR_INVALID, "SB_OPT_GRAM_TERMS must be 1 or 3");
@@ -191,6 +196,7 @@ extern "C" int32_t sb_maha_set_option(sb_maha_t* h, int32_t option, int64_t valu
 
 extern "C" int32_t sb_maha_pass1_stats(sb_maha_t* h, const float* d_X, int64_t rows, int64_t ld, void* d_ws,
                                        uint64_t ws_bytes, double* d_stats_out, uintptr_t stream) {
+  SB_RANGE("sb_maha_pass1_stats");
   SB_REQUIRE(h && rows >= 0 && (rows == 0 || (d_X && ld >= h->d)), SB_ERR_INVALID, "sb_maha_pass1_stats: bad arguments");
   SB_REQUIRE(h->stage == 0, SB_ERR_STATE, "sb_maha_pass1_stats: previous batch not committed");
   MahaWs ws;
@@ -226,6 +232,7 @@ extern "C" int32_t sb_maha_pass1_stats(sb_maha_t* h, const float* d_X, int64_t r
 extern "C" int32_t sb_maha_finalize(sb_maha_t* h, const double* d_all_stats, int32_t nranks, int32_t rank,
                                     int64_t total_rows, int64_t row0, void* d_ws, uint64_t ws_bytes,
                                     uintptr_t stream) {
+  SB_RANGE("sb_maha_finalize");
   SB_REQUIRE(h && nranks >= 1 && rank >= 0 && rank < nranks, SB_ERR_INVALID, "sb_maha_finalize: bad arguments");
   SB_REQUIRE(h->stage == 1, SB_ERR_STATE, "sb_maha_finalize: call sb_maha_pass1_stats first");
   SB_REQUIRE(total_rows >= 1 && (h->rows_local > 0 || (d_all_stats && nranks > 1)), SB_ERR_INVALID,
@@ -249,6 +256,7 @@ extern "C" int32_t sb_maha_finalize(sb_maha_t* h, const double* d_all_stats, int
 
 extern "C" int32_t sb_maha_pass2_score(sb_maha_t* h, const float* d_X, int64_t rows, int64_t ld, float* d_score,
                                        int32_t* d_flag, void* d_ws, uint64_t ws_bytes, uintptr_t stream) {
+  SB_RANGE("sb_maha_pass2_score");
   SB_REQUIRE(h && (rows == 0 || (d_X && d_score && d_flag && ld >= h->d)), SB_ERR_INVALID, "sb_maha_pass2_score: bad arguments");
   SB_REQUIRE(h->stage == 2, SB_ERR_STATE, "sb_maha_pass2_score: call sb_maha_finalize first");
   SB_REQUIRE(rows == h->rows_local, SB_ERR_INVALID, "sb_maha_pass2_score: rows differ from pass 1");
@@ -269,6 +277,7 @@ extern "C" int32_t sb_maha_pass2_score(sb_maha_t* h, const float* d_X, int64_t r
 }
 
 extern "C" int32_t sb_maha_commit(sb_maha_t* h, uintptr_t stream) {
+  SB_RANGE("sb_maha_commit");
   SB_REQUIRE(h, SB_ERR_INVALID, "sb_maha_commit: null handle");
   SB_REQUIRE(h->stage >= 2, SB_ERR_STATE, "sb_maha_commit: nothing to commit");
   cudaStream_t st = (cudaStream_t)stream;
@@ -291,6 +300,7 @@ extern "C" int32_t sb_maha_commit(sb_maha_t* h, uintptr_t stream) {
 
 extern "C" int32_t sb_maha_batch(sb_maha_t* h, const float* d_X, int64_t rows, int64_t ld, float* d_score,
                                  int32_t* d_flag, void* d_ws, uint64_t ws_bytes, uintptr_t stream) {
+  SB_RANGE("sb_maha_batch");
   int rc;
   if ((rc = sb_maha_pass1_stats(h, d_X, rows, ld, d_ws, ws_bytes, nullptr, stream))) return rc;
   if ((rc = sb_maha_finalize(h, nullptr, 1, 0, rows, 0, d_ws, ws_bytes, stream))) { h->stage = 0; return rc; }
@@ -299,12 +309,14 @@ extern "C" int32_t sb_maha_batch(sb_maha_t* h, const float* d_X, int64_t rows, i
 }
 
 extern "C" int32_t sb_maha_abort_batch(sb_maha_t* h) {
+  SB_RANGE("sb_maha_abort_batch");
   if (h) h->stage = 0;
   return SB_OK;
 }
 
 extern "C" int32_t sb_maha_get_state(sb_maha_t* h, double* h_mean, double* h_C, double* h_clip_lo, double* h_clip_hi,
                                      int64_t* n, int32_t* has_state, int32_t* has_clip, uintptr_t stream) {
+  SB_RANGE("sb_maha_get_state");
   SB_REQUIRE(h, SB_ERR_INVALID, "sb_maha_get_state: null handle");
   cudaStream_t st = (cudaStream_t)stream;
   const size_t d = h->d;
@@ -322,6 +334,7 @@ extern "C" int32_t sb_maha_get_state(sb_maha_t* h, double* h_mean, double* h_C, 
 extern "C" int32_t sb_maha_set_state(sb_maha_t* h, const double* h_mean, const double* h_C, const double* h_clip_lo,
                                      const double* h_clip_hi, int64_t n, int32_t has_state, int32_t has_clip,
                                      uintptr_t stream) {
+  SB_RANGE("sb_maha_set_state");
   SB_REQUIRE(h && n >= 0, SB_ERR_INVALID, "sb_maha_set_state: bad arguments");
   SB_REQUIRE(!has_state || (h_mean && h_C), SB_ERR_INVALID, "sb_maha_set_state: mean and C required");
   SB_REQUIRE(!has_clip || (h_clip_lo && h_clip_hi), SB_ERR_INVALID, "sb_maha_set_state: clip bounds required");
@@ -349,6 +362,7 @@ extern "C" int32_t sb_maha_set_state(sb_maha_t* h, const double* h_mean, const d
 
 extern "C" int32_t sb_maha_last_batch_sums(sb_maha_t* h, int64_t* n_flagged, double* score_sum, int64_t* gate_row,
                                            uintptr_t stream) {
+  SB_RANGE("sb_maha_last_batch_sums");
   SB_REQUIRE(h, SB_ERR_INVALID, "sb_maha_last_batch_sums: null handle");
   cudaStream_t st = (cudaStream_t)stream;
   long long g[5];
@@ -363,6 +377,7 @@ extern "C" int32_t sb_maha_last_batch_sums(sb_maha_t* h, int64_t* n_flagged, dou
 }
 
 extern "C" int32_t sb_maha_kernel_times(sb_maha_t* h, float* out_ms5, uintptr_t stream) {
+  SB_RANGE("sb_maha_kernel_times");
   SB_REQUIRE(h && out_ms5, SB_ERR_INVALID, "sb_maha_kernel_times: bad arguments");
   SB_REQUIRE(h->profile, SB_ERR_STATE, "sb_maha_kernel_times: enable SB_OPT_PROFILE first");
   SB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
@@ -371,6 +386,7 @@ extern "C" int32_t sb_maha_kernel_times(sb_maha_t* h, float* out_ms5, uintptr_t 
 }
 
 extern "C" int32_t sb_maha_debug_counters(sb_maha_t* h, int64_t* out8, uintptr_t stream) {
+  SB_RANGE("sb_maha_debug_counters");
   SB_REQUIRE(h && out8, SB_ERR_INVALID, "sb_maha_debug_counters: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
   long long g[8];
@@ -388,6 +404,7 @@ extern "C" int32_t sb_maha_debug_counters(sb_maha_t* h, int64_t* out8, uintptr_t
 }
 
 extern "C" int32_t sb_maha_get_eigvecs(sb_maha_t* h, double* h_V, uintptr_t stream) {
+  SB_RANGE("sb_maha_get_eigvecs");
   SB_REQUIRE(h && h_V, SB_ERR_INVALID, "sb_maha_get_eigvecs: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
   const size_t n = (size_t)h->d * h->KP;

@@ -686,6 +686,7 @@ int noalloc_scratch(float** out) {
 
 extern "C" int32_t sb_gram_stats_noalloc(const float* d_X, int64_t rows, int32_t d, int64_t ld, const float* d_shift,
                                          double* d_stats_out, uintptr_t stream) {
+  SB_RANGE("sb_gram_stats_noalloc");
   using namespace sb;
   SB_REQUIRE(d_X && d_shift && d_stats_out, SB_ERR_INVALID, "sb_gram_stats_noalloc: null pointer");
   SB_REQUIRE(d >= 1 && d <= kNoAllocMaxD, SB_ERR_INVALID,

@@ -537,7 +537,8 @@ __global__ void __launch_bounds__(kRouterThreads)
 router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long T,
                   const long long* __restrict__ rows, const float* __restrict__ reward,
                   const float* __restrict__ arm_p, int reward_mode, int* __restrict__ decisions, int forced_arm,
-                  double forced_reward, long long forced_rows, int dbg_fallback_period) {
+                  double forced_reward, long long forced_rows, int dbg_fallback_period, int pre_arm,
+                  double pre_reward, long long pre_rows) {
   constexpr int kind = KIND;
   __shared__ uint32_t s_py[MT_N], s_np[MT_N], s_np2[MT_N];
   __shared__ double s_U[kWinD + 2], s_gret[kWinD], s_gcache[kWinD], s_E[kWinD];
@@ -590,9 +591,14 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
   // room one beta draw may need: two gammas, each a few doubles per trial; a refill is forced below this margin
   constexpr int kArmMargin = 48;
   int win_built = 0;
-  for (long long t = 0; t < T; ++t) {
+  // pre_arm >= 0: one feedback (for a call routed by an earlier launch) is applied before the T calls of this launch -
+  // send_feedback followed by the next route() of the class API costs one launch instead of two
+  for (long long t = pre_arm >= 0 ? -1 : 0; t < T; ++t) {
+    const bool pre = t < 0;
     int arm;
-    if (forced_arm >= 0) {
+    if (pre) {
+      arm = pre_arm;
+    } else if (forced_arm >= 0) {
       arm = forced_arm;  // send_feedback for a call routed earlier
     } else if (kind == 0) {
       const double x = mt_double(py);  // EpsilonGreedy.py:90
@@ -750,11 +756,12 @@ router_run_kernel(RouterState* __restrict__ st, int n, double epsilon, long long
           for (int j = lane; j < n; j += 32) st->last_values[j] = s_num[j];
       }
     }
-    if (lane == 0 && forced_arm < 0) decisions[t] = arm;
-    if (reward_mode < 0) continue;
-    const long long nrows = forced_arm >= 0 ? forced_rows : (rows ? rows[t] : 1);
+    if (lane == 0 && forced_arm < 0 && !pre) decisions[t] = arm;
+    if (reward_mode < 0 && !pre) continue;
+    const long long nrows = pre ? pre_rows : (forced_arm >= 0 ? forced_rows : (rows ? rows[t] : 1));
     double r;
-    if (forced_arm >= 0) r = forced_reward;
+    if (pre) r = pre_reward;
+    else if (forced_arm >= 0) r = forced_reward;
     else if (reward_mode == 0) r = (double)reward[t];
     else if (reward_mode == 1) r = (double)reward[t * n + arm];
     else r = reward[t] < arm_p[arm] ? 1.0 : 0.0;
@@ -846,6 +853,7 @@ struct sb_router {
 
 extern "C" int32_t sb_router_create(sb_router_t** out, int32_t kind, int32_t n_branches, double epsilon, int64_t seed,
                                     int32_t best_branch) {
+  SB_RANGE("sb_router_create");
   SB_REQUIRE(out, SB_ERR_INVALID, "sb_router_create: null handle pointer");
   SB_REQUIRE(kind == SB_ROUTER_EPSILON_GREEDY || kind == SB_ROUTER_THOMPSON, SB_ERR_INVALID, "sb_router_create: bad kind");
   SB_REQUIRE(n_branches > 0 && n_branches <= kMaxArms, SB_ERR_INVALID, "n_branches parameter must be given (1..%d)", kMaxArms);
@@ -902,6 +910,7 @@ extern "C" int32_t sb_router_create(sb_router_t** out, int32_t kind, int32_t n_b
 }
 
 extern "C" int32_t sb_router_destroy(sb_router_t* h) {
+  SB_RANGE("sb_router_destroy");
   if (!h) return SB_OK;
   cudaFree(h->d_state);
   cudaFreeHost(h->h_decision);
@@ -911,6 +920,7 @@ extern "C" int32_t sb_router_destroy(sb_router_t* h) {
 
 extern "C" int32_t sb_router_run(sb_router_t* h, int64_t T, const int64_t* d_rows_per_call, const float* d_reward,
                                  const float* d_arm_p, int32_t reward_mode, int32_t* d_decisions, uintptr_t stream) {
+  SB_RANGE("sb_router_run");
   SB_REQUIRE(h && T >= 0 && reward_mode >= -1 && reward_mode <= 2, SB_ERR_INVALID, "sb_router_run: bad arguments");
   if (T == 0) return SB_OK;
   SB_REQUIRE(d_decisions, SB_ERR_INVALID, "sb_router_run: null decisions");
@@ -922,25 +932,26 @@ extern "C" int32_t sb_router_run(sb_router_t* h, int64_t T, const int64_t* d_row
     router_run_kernel<1><<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, (long long)T,
                                                                         (const long long*)d_rows_per_call, d_reward,
                                                                         d_arm_p, reward_mode, d_decisions, -1, 0.0, 0,
-                                                                        h->dbg_fallback_period);
+                                                                        h->dbg_fallback_period, -1, 0.0, 0);
   else
     router_run_kernel<0><<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, (long long)T,
                                                             (const long long*)d_rows_per_call, d_reward, d_arm_p,
-                                                            reward_mode, d_decisions, -1, 0.0, 0, 0);
+                                                            reward_mode, d_decisions, -1, 0.0, 0, 0, -1, 0.0, 0);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }
 
 extern "C" int32_t sb_router_feedback(sb_router_t* h, int32_t arm, int64_t rows, double reward, uintptr_t stream) {
+  SB_RANGE("sb_router_feedback");
   SB_REQUIRE(h && arm >= 0 && arm < h->n, SB_ERR_INVALID, "sb_router_feedback: routing %d outside 0..%d", arm,
              h ? h->n - 1 : 0);
   SB_REQUIRE(rows >= 1, SB_ERR_INVALID, "sb_router_feedback: rows must be >= 1 (reference divides by tries)");
   if (h->kind == SB_ROUTER_THOMPSON)
     router_run_kernel<1><<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, 1, nullptr, nullptr,
-                                                                        nullptr, 0, nullptr, arm, reward, (long long)rows, 0);
+                                                                        nullptr, 0, nullptr, arm, reward, (long long)rows, 0, -1, 0.0, 0);
   else
     router_run_kernel<0><<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, 1, nullptr, nullptr, nullptr, 0,
-                                                            nullptr, arm, reward, (long long)rows, 0);
+                                                            nullptr, arm, reward, (long long)rows, 0, -1, 0.0, 0);
   SB_LAUNCH_CHECK();
   return SB_OK;
 }
@@ -950,6 +961,7 @@ extern "C" int64_t sb_router_state_len(const sb_router_t* h) {
 }
 
 extern "C" int32_t sb_router_get_state(sb_router_t* h, int64_t* out, uintptr_t stream) {
+  SB_RANGE("sb_router_get_state");
   SB_REQUIRE(h && out, SB_ERR_INVALID, "sb_router_get_state: bad arguments");
   RouterState* hs = new RouterState();
   cudaStream_t st = (cudaStream_t)stream;
@@ -973,6 +985,7 @@ extern "C" int32_t sb_router_get_state(sb_router_t* h, int64_t* out, uintptr_t s
 }
 
 extern "C" int32_t sb_router_set_state(sb_router_t* h, const int64_t* in, uintptr_t stream) {
+  SB_RANGE("sb_router_set_state");
   SB_REQUIRE(h && in, SB_ERR_INVALID, "sb_router_set_state: bad arguments");
   RouterState* hs = new RouterState();
   memset(hs, 0, sizeof *hs);
@@ -996,6 +1009,7 @@ extern "C" int32_t sb_router_set_state(sb_router_t* h, const int64_t* in, uintpt
 }
 
 extern "C" int32_t sb_router_set_option(sb_router_t* h, int32_t option, int64_t value) {
+  SB_RANGE("sb_router_set_option");
   SB_REQUIRE(h, SB_ERR_INVALID, "sb_router_set_option: null handle");
   SB_REQUIRE(option == SB_ROUTER_OPT_DEBUG_FALLBACK_PERIOD && value >= 0 && value <= 0x7fffffff, SB_ERR_INVALID,
              "sb_router_set_option: unknown option %d or bad value", option);
@@ -1004,6 +1018,7 @@ extern "C" int32_t sb_router_set_option(sb_router_t* h, int32_t option, int64_t 
 }
 
 extern "C" int32_t sb_router_counters(sb_router_t* h, int64_t* out2, uintptr_t stream) {
+  SB_RANGE("sb_router_counters");
   SB_REQUIRE(h && out2, SB_ERR_INVALID, "sb_router_counters: bad arguments");
   long long v[2];
   cudaStream_t st = (cudaStream_t)stream;
@@ -1015,27 +1030,46 @@ extern "C" int32_t sb_router_counters(sb_router_t* h, int64_t* out2, uintptr_t s
 }
 
 // route() of the class API: one call, the decision written by the kernel into pinned host memory (no device buffer, no
-// copy), then a stream synchronisation.
-extern "C" int32_t sb_router_route(sb_router_t* h, int32_t* h_out, uintptr_t stream) {
+// copy), then a stream synchronisation.  pre_arm >= 0: the feedback of the previous request is applied first, in the
+// same launch.
+static int32_t router_route_impl(sb_router_t* h, int32_t pre_arm, int64_t pre_rows, double pre_reward, int32_t* h_out,
+                                 uintptr_t stream) {
   SB_REQUIRE(h && h_out, SB_ERR_INVALID, "sb_router_route: bad arguments");
   SB_REQUIRE(!(h->kind == SB_ROUTER_EPSILON_GREEDY && h->n < 2), SB_ERR_INVALID,
              "epsilon-greedy needs >= 2 branches to explore (reference raises IndexError on random.choice([]))");
+  SB_REQUIRE(pre_arm < h->n && (pre_arm < 0 || pre_rows >= 1), SB_ERR_INVALID,
+             "sb_router_feedback_route: routing %d outside 0..%d or rows < 1", pre_arm, h->n - 1);
   int* d_dec = nullptr;
   SB_CUDA(cudaHostGetDevicePointer((void**)&d_dec, h->h_decision, 0));
   if (h->kind == SB_ROUTER_THOMPSON)
     router_run_kernel<1><<<1, kRouterThreads, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, 1, nullptr, nullptr,
                                                                         nullptr, -1, d_dec, -1, 0.0, 0,
-                                                                        h->dbg_fallback_period);
+                                                                        h->dbg_fallback_period, pre_arm, pre_reward,
+                                                                        (long long)pre_rows);
   else
     router_run_kernel<0><<<1, 32, 0, (cudaStream_t)stream>>>(h->d_state, h->n, h->epsilon, 1, nullptr, nullptr, nullptr, -1,
-                                                            d_dec, -1, 0.0, 0, 0);
+                                                            d_dec, -1, 0.0, 0, 0, pre_arm, pre_reward,
+                                                            (long long)pre_rows);
   SB_LAUNCH_CHECK();
   SB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
   *h_out = *(volatile int*)h->h_decision;
   return SB_OK;
 }
 
+extern "C" int32_t sb_router_route(sb_router_t* h, int32_t* h_out, uintptr_t stream) {
+  SB_RANGE("sb_router_route");
+  return router_route_impl(h, -1, 0, 0.0, h_out, stream);
+}
+
+extern "C" int32_t sb_router_feedback_route(sb_router_t* h, int32_t arm, int64_t rows, double reward, int32_t* h_out,
+                                            uintptr_t stream) {
+  SB_RANGE("sb_router_feedback_route");
+  SB_REQUIRE(arm >= 0, SB_ERR_INVALID, "sb_router_feedback_route: routing %d outside 0..%d", arm, h ? h->n - 1 : 0);
+  return router_route_impl(h, arm, rows, reward, h_out, stream);
+}
+
 extern "C" int32_t sb_router_last_values(sb_router_t* h, double* h_values, uintptr_t stream) {
+  SB_RANGE("sb_router_last_values");
   SB_REQUIRE(h && h_values, SB_ERR_INVALID, "sb_router_last_values: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
   SB_CUDA(cudaMemcpyAsync(h_values, h->d_state->last_values, sizeof(double) * h->n, cudaMemcpyDeviceToHost, st));

@@ -47,6 +47,7 @@ class _RouterBase(object):
         self._h = None
         self._lock = threading.RLock()
         self._restore = None
+        self._pending = None   # (routing, rows, reward) of a send_feedback not yet launched: it rides with the next route
 
     # -- device handle
     def _handle(self):
@@ -56,6 +57,9 @@ class _RouterBase(object):
             if not torch.cuda.is_available():
                 raise SeldonB200Error("no CUDA device: seldon_core_b200 has no CPU fallback", status_code=500)
             if self._device is None:
+                self._device = torch.device("cuda", torch.cuda.current_device())
+            self._device = torch.device(self._device)
+            if self._device.index is None:
                 self._device = torch.device("cuda", torch.cuda.current_device())
             h = ctypes.c_void_p()
             with torch.cuda.device(self._device):
@@ -72,10 +76,21 @@ class _RouterBase(object):
 
         return torch.cuda.current_stream(self._device).cuda_stream
 
+    def _flush(self):
+        """Launch a feedback that was waiting for the next route (called before anything else touches the state)."""
+        import torch
+
+        if self._pending is not None:
+            routing, rows, reward = self._pending
+            self._pending = None
+            with torch.cuda.device(self._device):
+                _cabi.check(_cabi.lib().sb_router_feedback(self._handle(), routing, rows, reward, self._stream()))
+
     def _get_state(self):
         import torch
 
         h = self._handle()
+        self._flush()
         L = _cabi.lib()
         st = np.zeros(L.sb_router_state_len(h), dtype=np.int64)
         with torch.cuda.device(self._device):
@@ -104,8 +119,17 @@ class _RouterBase(object):
         with self._lock:
             h = self._handle()
             out = ctypes.c_int32()
-            with torch.cuda.device(self._device):
-                _cabi.check(_cabi.lib().sb_router_route(h, ctypes.byref(out), self._stream()))
+            L = _cabi.lib()
+            pend, self._pending = self._pending, None
+            if torch.cuda.current_device() != self._device.index:
+                torch.cuda.set_device(self._device)
+            st = self._stream()
+            if pend is None:
+                rc = L.sb_router_route(h, ctypes.byref(out), st)
+            else:  # the previous request's feedback and this route in one launch
+                rc = L.sb_router_feedback_route(h, pend[0], pend[1], pend[2], ctypes.byref(out), st)
+            if rc:
+                _cabi.check(rc)
             branch = int(out.value)
             if self.history:  # EpsilonGreedy.py:99-101, ThompsonSampling.py:88-90
                 self.branch_history.append(branch)
@@ -117,6 +141,8 @@ class _RouterBase(object):
         logarithms, and beta draws taken draw by draw outside the look-ahead window (include/sb200.h)."""
         import torch
 
+        self._handle()
+        self._flush()
         out = (ctypes.c_int64 * 2)()
         with torch.cuda.device(self._device):
             _cabi.check(_cabi.lib().sb_router_counters(self._handle(), out, self._stream()))
@@ -136,8 +162,16 @@ class _RouterBase(object):
 
         with self._lock:
             h = self._handle()
-            with torch.cuda.device(self._device):
-                _cabi.check(_cabi.lib().sb_router_feedback(h, int(routing), rows, float(reward), self._stream()))
+            routing = int(routing)
+            if not 0 <= routing < self.n_branches:
+                raise SeldonB200Error("send_feedback: routing %d outside 0..%d" % (routing, self.n_branches - 1))
+            if rows < 1:
+                raise SeldonB200Error("send_feedback: rows must be >= 1 (reference divides by tries)")
+            self._flush()
+            # not launched yet: the next route() applies it in its own launch (sb_router_feedback_route); anything else
+            # that reads or changes the state flushes it first
+            self._pending = (routing, rows, float(reward))
+            del h
 
     def n_success_failures(self, features, reward):
         n_predictions = features.shape[0]
@@ -151,6 +185,7 @@ class _RouterBase(object):
 
         with self._lock:
             h = self._handle()
+            self._flush()
             dev = self._device
 
             def to_dev(a, dt):
@@ -173,13 +208,16 @@ class _RouterBase(object):
     # -- persistence (python/seldon_core/persistence.py:84): bandit state and both generator positions
     def __getstate__(self):
         with self._lock:
-            out = {k: v for k, v in self.__dict__.items() if k not in ("_h", "_lock", "_device", "_restore")}
+            out = {k: v for k, v in self.__dict__.items() if k not in ("_h", "_lock", "_device", "_restore", "_pending")}
             out["_saved"] = self._get_state() if self._h is not None else self._restore
+            out["_pending_saved"] = None
             return out
 
     def __setstate__(self, state):
         saved = state.pop("_saved")
+        state.pop("_pending_saved", None)
         self.__dict__.update(state)
+        self._pending = None
         self._h = None
         self._device = None
         self._lock = threading.RLock()
@@ -225,7 +263,8 @@ class ThompsonSamplingB200(_RouterBase):
         import torch
 
         v = np.zeros(self.n_branches)
-        with torch.cuda.device(self._device if self._device is not None else 0):
+        self._handle()
+        with torch.cuda.device(self._device):
             _cabi.check(_cabi.lib().sb_router_last_values(self._handle(), v.ctypes.data, self._stream()))
         return v.tolist()
 

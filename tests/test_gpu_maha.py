@@ -310,3 +310,32 @@ def test_subspace_iteration_falls_back_without_a_gap():
         if i > 0:
             assert _counters(a)[7] < 0
         assert np.array_equal(pa, pb) and rel_err(a.score, b.score).max() < 1e-5
+
+
+def test_cold_start_relaxed_region_report(capsys):
+    """How much of a cold batch is held to the relaxed tolerance, and how bad it gets there: the
+    rows between the opening of the warm-up gate and 12 k rows later, on a batch that starts from an empty state.
+    Printed for the record (DESIGN.md section 2 quotes it) and bounded."""
+    k, d, rows = 16, 64, 200000
+    worst_loose, worst_strict, n_loose, gates = 0.0, 0.0, 0, []
+    for seed in (101, 102, 103):
+        X, _ = synth.maha_rows_numpy(rows, d, k, seed=seed)
+        det, ref = OutlierMahalanobisB200(n_components=k), MahalanobisLean(n_components=k)
+        det.predict(X, None), ref.predict(X.astype(np.float64), None)
+        err = rel_err(det.score, ref.score)
+        first_open = int(np.flatnonzero(ref.score)[0])
+        settle = first_open + 12 * k
+        assert np.all(det.score[:first_open] == 0.0)
+        gates.append(first_open)
+        n_loose += settle - first_open
+        worst_loose = max(worst_loose, float(err[first_open:settle].max()))
+        worst_strict = max(worst_strict, float(err[settle:].max()))
+        thr = det.threshold
+        safe = np.abs(ref.score - thr) > 2 * TOL * thr
+        safe[first_open:settle] &= np.abs(ref.score[first_open:settle] - thr) > 0.1 * thr
+        assert np.array_equal(det.prediction[safe], ref.prediction[safe])
+    with capsys.disabled():
+        print("cold start, d=%d k=%d, %d-row batches: gate opens at rows %s; %d of %d rows per batch (%.4f %%) are in the "
+              "relaxed region; worst relative score error there %.2e (bound 5e-2), after it %.2e (bound 1e-4)"
+              % (d, k, rows, gates, n_loose // 3, rows, 100.0 * n_loose / 3 / rows, worst_loose, worst_strict))
+    assert worst_loose < 5e-2 and worst_strict < TOL
