@@ -117,6 +117,7 @@ __device__ int32_t parse_number(const uint8_t* s, int avail, double* out) {
       else { ++exp10; trunc |= dgt != 0; }
     }
     if (ndig == 0) return JSON_MALFORMED;
+    if (ndig > 1 && s[p - ndig] == '0') return JSON_MALFORMED;  // JSON has no leading zeros ("01" is not a number)
     if (p < avail && s[p] == '.') {
       ++p;
       int nfrac = 0;
@@ -152,11 +153,12 @@ __device__ int32_t parse_number(const uint8_t* s, int avail, double* out) {
 }
 
 // character classes through a 256-byte table in shared memory: one load per text byte instead of a dozen compares
-constexpr uint8_t kClsToken = 1, kClsOther = 2, kClsOpen = 4, kClsClose = 8;
+constexpr uint8_t kClsToken = 1, kClsOther = 2, kClsOpen = 4, kClsClose = 8, kClsComma = 16, kClsSpace = 32;
 __device__ __forceinline__ void fill_class_table(uint8_t* lut) {
   for (int c = threadIdx.x; c < 256; c += blockDim.x)
     lut[c] = (uint8_t)((token_char((uint8_t)c) ? kClsToken : 0) | (other_char((uint8_t)c) ? kClsOther : 0) |
-                       (c == '[' ? kClsOpen : 0) | (c == ']' ? kClsClose : 0));
+                       (c == '[' ? kClsOpen : 0) | (c == ']' ? kClsClose : 0) | (c == ',' ? kClsComma : 0) |
+                       (space_char((uint8_t)c) ? kClsSpace : 0));
 }
 // classes of this thread's kJsonPer (= 16) bytes and of the byte before them
 __device__ __forceinline__ void classify16(const uint8_t* t, int i0, const uint8_t* lut, uint8_t (&cls)[kJsonPer],
@@ -268,16 +270,18 @@ json_parse(const uint8_t* __restrict__ text, uint64_t nbytes, const int64_t* __r
   const uint8_t* t = sm + 16;
   const int64_t lim = min((int64_t)kJsonChunk, (int64_t)nbytes - ch * (int64_t)kJsonChunk);
   const int i0 = threadIdx.x * kJsonPer;
-  // token starts and inner '[' among this thread's bytes, as bit masks
-  uint32_t starts = 0, opens = 0;
+  // token starts and inner '[' among this thread's bytes, as bit masks; `gram` marks every character whose left
+  // neighbour (white space skipped) the array grammar constrains: number starts, ',', '[' and ']'
+  uint32_t starts = 0, opens = 0, gram = 0;
   {
     uint8_t cls[kJsonPer], prev;
     classify16(t, i0, lut, cls, prev);
 #pragma unroll
     for (int k = 0; k < kJsonPer; ++k) {
       const bool live = i0 + k < lim;
-      if (live && (cls[k] & kClsToken) && !(prev & kClsToken)) starts |= 1u << k;
+      if (live && (cls[k] & kClsToken) && !(prev & kClsToken)) { starts |= 1u << k; gram |= 1u << k; }
       if (live && (cls[k] & kClsOpen) && ch * (int64_t)kJsonChunk + i0 + k != 0) opens |= 1u << k;
+      if (live && (cls[k] & (kClsOpen | kClsClose | kClsComma))) gram |= 1u << k;
       prev = cls[k];
     }
   }
@@ -296,6 +300,39 @@ json_parse(const uint8_t* __restrict__ text, uint64_t nbytes, const int64_t* __r
   for (int w = 0; w < warp; ++w) before += warp_tok[w];
   int64_t k = chunk_prefix[ch] + before;  // global index of this thread's first token
   int32_t bad = JSON_OK;
+  // The array grammar, as a condition on the nearest non-blank character to the left of every number start and of
+  // every structural character (what json.loads enforces, utils.py:499-505 -> json.loads):
+  //   number : '[' or ','          ','  : the end of a number or ']'
+  //   '['    : '[' or ',' (or the first character)      ']' : the end of a number, ']' or '[' (an empty list)
+  // Together with the bracket counts checked by the caller this rejects "[[1 2]]", "[[1,,2]]", "[1,2,]", "[,1]", ...
+  while (gram) {
+    const int j = __ffs((int)gram) - 1;
+    gram &= gram - 1;
+    const int i = i0 + j;
+    const int64_t gpos = ch * (int64_t)kJsonChunk + i;
+    if (gpos == 0) continue;  // the opening bracket of the whole array
+    int q = i - 1;
+    uint8_t pc = 0;
+    bool found = false;
+    for (; q >= -16; --q) {
+      pc = t[q];
+      if (!(lut[pc] & kClsSpace)) { found = true; break; }
+    }
+    if (!found) {  // a run of more than 16 blanks reaches back past the staged bytes: read the text itself
+      for (int64_t g = ch * (int64_t)kJsonChunk - 17; g >= 0; --g) {
+        pc = text[g];
+        if (!(lut[pc] & kClsSpace)) { found = true; break; }
+      }
+    }
+    const uint8_t me = lut[t[i]], pl = found ? lut[pc] : 0;
+    const bool p_open = pl & kClsOpen, p_close = pl & kClsClose, p_comma = pl & kClsComma, p_num = pl & kClsToken;
+    bool ok;
+    if (me & kClsToken) ok = p_open || p_comma;
+    else if (me & kClsComma) ok = p_num || p_close;
+    else if (me & kClsOpen) ok = p_open || p_comma;
+    else ok = p_num || p_close || p_open;
+    if (!found || !ok) bad = JSON_MALFORMED;
+  }
   // an inner row opens at every '[' but the first: everything before it must be whole rows
   while (opens) {
     const int j = __ffs((int)opens) - 1;

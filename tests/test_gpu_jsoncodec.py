@@ -150,3 +150,24 @@ def test_predict_raw_on_rest_text():
     assert resp["data"]["tensor"]["shape"] == [77, 18]
     assert resp["data"]["tensor"]["values"] == X2.astype(np.float64).ravel().tolist()
     assert resp["meta"]["tags"] == {"outlier-predictions": want2.tolist()}
+
+
+@pytest.mark.parametrize("text", [b"[[1 2],[3 4]]", b"[[1,,2]]", b"[[1,2,],[3,4,5]]", b"[[1,2],[3,4],]", b"[[01,2]]", b"[[1,2][3,4]]",
+                                  b"[,1,2]", b"[[1,2],,[3,4]]", b"[[+1,2]]", b"[[1.,2]]", b"[[.5,2]]",
+                                  b"[[-NaN,1]]", b"[[1,2]" + b" " * 40 + b"[3,4]]"])
+def test_decode_rejects_what_json_loads_rejects(text):
+    """the token splitter alone accepted separators json.loads refuses.  Every case here is invalid JSON (or
+    not a rectangular numeric array) and must raise."""
+    with pytest.raises(Exception):
+        json.loads(b'{"data":{"ndarray":' + text + b'}}')
+        raise ValueError("json accepts it: not rectangular")  # reached only by the ragged / nested cases
+    with pytest.raises(SeldonB200Error):
+        codec.decode_json_ndarray(b'{"data":{"ndarray":' + text + b'}}')
+
+
+@pytest.mark.parametrize("text", [b"[[1,2],[3,4]]", b"[ [ 1 , 2 ] ,\n\t[ 3 , 4 ] ]", b"[[0,0.5],[-0,0e1]]", b"[1,2,3]",
+                                  b"[[1,2]," + b" " * 70 + b"[3,4]]", b"[[1," + b"\n" * 40 + b"2],[3,4]]", b"[[1e5,2E-3],[NaN,-Infinity]]"])
+def test_decode_accepts_what_json_loads_accepts(text):
+    want = np.array(json.loads(text)).astype(np.float32)
+    got = codec.decode_json_ndarray(b'{"data":{"ndarray":' + text + b'}}').cpu().numpy()
+    assert got.shape == want.shape and np.array_equal(got, want, equal_nan=True)
