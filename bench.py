@@ -134,8 +134,6 @@ def cpu_graph(steps=1, warmup=0, budget_s=150.0):
     from oracle.combiner import mean_combiner
     from seldon_core_b200 import synth
 
-    if os.environ.get("OMP_NUM_THREADS") == "1" and "SB200_KEEP_OMP" not in os.environ:
-        pass  # torchrun pins OMP_NUM_THREADS=1 for its workers; BLAS was already loaded with it - reported as is
     if ref_shim.available():
         det = ref_shim.core_mahalanobis_class()(n_components=K_COMP)
         kind = "reference"
@@ -207,6 +205,11 @@ def cpu_restatement_full(rows=ROWS_PER_GPU):
 def run_reference(args, rank, world):
     if rank != 0:
         return
+    # torchrun pins OMP_NUM_THREADS=1 for its workers; the CPU arm is meant to use every host thread it can, and
+    # numpy / BLAS have not been loaded yet in this process
+    if "numpy" not in sys.modules and os.environ.get("OMP_NUM_THREADS") == "1" and world > 1:
+        for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+            os.environ[var] = str(os.cpu_count() or 1)
     steps = max(1, args.steps)
     info, sec_per_step, done = cpu_graph(steps=steps, warmup=min(args.warmup, 1))
     line = {"impl": "reference", "metric": METRIC, "value": info["value"], "unit": UNIT, "n_gpus": args.gpus,
@@ -481,8 +484,23 @@ def block_codec(dev, hbm):
     assert int(status.item()) == 0
     out["unpack_json_ndarray"] = hbm_line(nbytes + 4 * rows * cols, med, hbm)
     out["unpack_json_ndarray"]["values_per_s"] = rows * cols / (med * 1e-3)
+    # fp32 matrix -> the text json.dumps writes (shortest round-trip decimals)
+    x = torch.randn((rows, cols), device=dev)
+    cap = int(L.sb_json_text_capacity(rows, cols))
+    text = torch.empty(cap, dtype=torch.uint8, device=dev)
+    ews = torch.empty((int(L.sb_json_encode_workspace_bytes(rows, cols)) + 7) // 8, dtype=torch.int64, device=dev)
+    nb_out = torch.zeros(1, dtype=torch.int64, device=dev)
+    f_enc = lambda: _cabi.check(L.sb_pack_json_ndarray(x.data_ptr(), 0, rows, cols, ews.data_ptr(), ews.numel() * 8,
+                                                       text.data_ptr(), nb_out.data_ptr(), st))
+    _, med = timed_events(f_enc)
+    tlen = int(nb_out.item())
+    out["pack_json_ndarray"] = hbm_line(tlen + 4 * rows * cols, med, hbm)
+    out["pack_json_ndarray"]["values_per_s"] = rows * cols / (med * 1e-3)
+    out["pack_json_ndarray"]["text_bytes_per_value"] = tlen / (rows * cols)
+    sizes = {"pack_tensor": 1 << 28, "unpack_tensor": 1 << 28, "pack_listvalue": 1 << 27, "unpack_listvalue": 1 << 27}
     for k, v in out.items():
-        v["values_per_s"] = v.get("values_per_s", None)
+        if "values_per_s" not in v:
+            v["values_per_s"] = sizes[k] / (v["ms"] * 1e-3)
     return out
 
 

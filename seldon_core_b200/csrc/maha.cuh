@@ -38,6 +38,7 @@ int64_t max_subsegments(int64_t max_rows);
 constexpr int kTargetChains2 = kNumSMs * 64;  // 2 CTAs x 4 warps x 8 chains per SM
 constexpr int kMinSubLen2 = 256;
 SubLayout make_layout2(int64_t rows);
+SubLayout make_layout1(int64_t rows);
 int64_t max_subsegments2(int64_t max_rows);
 
 constexpr int SUBFLAG_OPEN = 1;  // warm-up gate test passes at the first row of the sub-segment

@@ -220,6 +220,7 @@ extern "C" int32_t sb_maha_pass1_stats(sb_maha_t* h, const float* d_X, int64_t r
   h->split_pass2 = h->KP == 16 && (h->d == 64 || h->d == 128 || h->d == 256) && !h->force_generic &&
                    !h->fused_pass2 && (ld % 4 == 0) && (((uintptr_t)d_X & 15) == 0);
   h->lay2 = h->split_pass2 ? make_layout2(rows) : h->lay;
+  if (h->split_pass2) h->lay = make_layout1(rows);  // fewer, longer pass-1 sub-segments: the partials are only summed
   SB_REQUIRE(h->d_in_mu == nullptr || (h->split_pass2 && !h->legacy_mma), SB_ERR_INVALID,
              "sb_maha_pass1_stats: the fused input transform needs the tensor-core path (d = 64, 128 or 256, "
              "n_components <= 16, 16-byte aligned rows, no SB_OPT_FORCE_GENERIC / FUSED_PASS2 / LEGACY_MMA)");

@@ -1487,22 +1487,44 @@ chain4(const float* __restrict__ Zp, const float* __restrict__ Dp, const uint8_t
   }
 }
 
-// PC0 = V^T C0 V (KP x KP, zero padded), one block
+// PC0 = V^T C0 V (KP x KP, zero padded), one block.  T = C0 V first: C0 is symmetric, so thread (feature f, column
+// group) walks column f of C0 - consecutive threads read consecutive addresses - with the rows of V broadcast from
+// shared memory; the loads are independent of the accumulation and pipeline freely (the first version read C0 by rows,
+// two distinct addresses per warp load: 150 us at d = 256, a visible part of a 2 Mi-row shard's batch).
 __global__ void __launch_bounds__(1024)
-project_cov(const double* __restrict__ C0, const double* __restrict__ V, int d, int KP, double* __restrict__ PC0) {
-  extern __shared__ double T[];  // [d][KP] = C0 V
-  for (int idx = threadIdx.x; idx < d * KP; idx += blockDim.x) {
-    const int f = idx / KP, c = idx - f * KP;
-    double acc = 0.0;
-    for (int g = 0; g < d; ++g) acc = fma(C0[(size_t)f * d + g], V[(size_t)g * KP + c], acc);
-    T[idx] = acc;
+project_cov(const double* __restrict__ C0, const double* __restrict__ V, int d, int KP, double* __restrict__ PC0,
+            int stage_v) {
+  extern __shared__ double T[];  // [d][KP] = C0 V, then (where it fits) [d][KP] V staged behind it
+  const double* Vs = V;
+  if (stage_v) {
+    double* vs = T + (size_t)d * KP;
+    for (int idx = threadIdx.x; idx < d * KP; idx += blockDim.x) vs[idx] = V[idx];
+    Vs = vs;
+    __syncthreads();
+  }
+  const int ngrp = KP / 4;  // KP is 4, 8, 16 or 32: four columns per thread
+  for (int idx = threadIdx.x; idx < d * ngrp; idx += blockDim.x) {
+    const int f = idx % d, c0 = 4 * (idx / d);
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll 8
+    for (int g = 0; g < d; ++g) {
+      const double c = C0[(size_t)g * d + f];
+      const double* v = Vs + g * KP + c0;
+      a0 = fma(c, v[0], a0); a1 = fma(c, v[1], a1); a2 = fma(c, v[2], a2); a3 = fma(c, v[3], a3);
+    }
+    double* t = T + f * KP + c0;
+    t[0] = a0; t[1] = a1; t[2] = a2; t[3] = a3;
   }
   __syncthreads();
   for (int idx = threadIdx.x; idx < KP * KP; idx += blockDim.x) {
     const int a = idx / KP, b = idx - a * KP;
-    double acc = 0.0;
-    for (int f = 0; f < d; ++f) acc = fma(V[(size_t)f * KP + a], T[f * KP + b], acc);
-    PC0[idx] = acc;
+    double acc0 = 0.0, acc1 = 0.0;
+    for (int f = 0; f + 1 < d; f += 2) {
+      acc0 = fma(Vs[f * KP + a], T[f * KP + b], acc0);
+      acc1 = fma(Vs[(f + 1) * KP + a], T[(f + 1) * KP + b], acc1);
+    }
+    if (d & 1) acc0 = fma(Vs[(d - 1) * KP + a], T[(d - 1) * KP + b], acc0);
+    PC0[idx] = acc0 + acc1;
   }
 }
 
@@ -1515,8 +1537,10 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
   const int KQ = KP + KP * KP;
   const size_t PS = (size_t)d + (size_t)d * d;
   if (h->profile) cudaEventRecord(h->ev[4], st);
-  SB_CUDA(cudaFuncSetAttribute(project_cov, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxD * kMaxKP * 8));
-  project_cov<<<1, 1024, (size_t)d * KP * sizeof(double), st>>>(h->d_C, h->d_V, d, KP, h->d_PC0);
+  const int stage_v = (size_t)2 * d * KP * sizeof(double) <= 200 * 1024;
+  const size_t pc_smem = (size_t)(stage_v ? 2 : 1) * d * KP * sizeof(double);
+  SB_CUDA(cudaFuncSetAttribute(project_cov, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  project_cov<<<1, 1024, pc_smem, st>>>(h->d_C, h->d_V, d, KP, h->d_PC0, stage_v);
   SB_LAUNCH_CHECK();
   int grid = nsub < kNumSMs * 8 ? nsub : kNumSMs * 8;
   const int FC = d < 8192 / d ? d : 8192 / d;

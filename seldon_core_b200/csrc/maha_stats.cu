@@ -51,6 +51,11 @@ int64_t max_subs_for(int64_t max_rows, int64_t target, int64_t minlen) {
 SubLayout make_layout(int64_t rows) { return layout_for(rows, kTargetChains, kMinSubLen); }
 int64_t max_subsegments(int64_t max_rows) { return max_subs_for(max_rows, kTargetChains, kMinSubLen); }
 SubLayout make_layout2(int64_t rows) { return layout_for(rows, kTargetChains2, kMinSubLen2); }
+// Pass 1 of the split path: its partials are only ever summed (pass 2 takes its per-sub-segment statistics from the
+// projection kernel), so it needs no more sub-segments than keep the persistent CTAs busy and an fp32 accumulation
+// short (kMaxSubLen rows): a multiple of the SM count.  At d = 256 a partial is 263 KB - 2368 of them per batch were
+// 623 MB written and read back, a third of the input of a 2 Mi-row shard.
+SubLayout make_layout1(int64_t rows) { return layout_for(rows, kNumSMs, kMinSubLen); }
 int64_t max_subsegments2(int64_t max_rows) { return max_subs_for(max_rows, kTargetChains2, kMinSubLen2); }
 
 namespace {
