@@ -367,8 +367,14 @@ pass1_gram_umma(const float* __restrict__ X, int64_t ld, SubLayout lay, const fl
           for (int e = 0; e < 4; ++e) {
             if (CLIP) v[e] = fminf(fmaxf(v[e], ll[e]), hh[e]);
             const float dv = valid ? v[e] - mm[e] : 0.f;
-            hi4[e] = round_tf32(dv);
-            if (TERMS == 3) lo4[e] = round_tf32(dv - __uint_as_float(hi4[e]));
+            if (TERMS == 3) {
+              // split by truncation: the tensor core reads the top 19 bits of a tf32 operand and ignores the rest, so
+              // "hi" is the value as it is and "lo" what the truncation drops (exact; itself truncated by the hardware)
+              hi4[e] = __float_as_uint(dv);
+              lo4[e] = __float_as_uint(dv - __uint_as_float(hi4[e] & 0xffffe000u));
+            } else {
+              hi4[e] = round_tf32(dv);  // a single term keeps round-to-nearest: its error is the whole error
+            }
             v[e] = dv;
           }
           sums[i].x += v[0]; sums[i].y += v[1]; sums[i].z += v[2]; sums[i].w += v[3];
