@@ -504,6 +504,33 @@ def block_codec(dev, hbm):
     return out
 
 
+def block_latency(dev):
+    """Request latency of the wire path: `predict_raw` on small serialised requests (1, 100 and 10 000 rows x 64, f64
+    Tensor), wall clock per call, median of 200 - the regime the reference's wrapper serves most of the time."""
+    import numpy as np
+
+    from seldon_core_b200 import OutlierMahalanobisB200, synth, wire
+
+    det = OutlierMahalanobisB200(n_components=K_COMP, device=dev)
+    prime, _ = synth.maha_rows_numpy(20000, D, K_COMP, seed=101)
+    det.predict(prime, None)
+    out = {}
+    for rows in (1, 100, 10000):
+        X, _ = synth.maha_rows_numpy(rows, D, K_COMP, seed=7 + rows)
+        req = wire.make_tensor_request_pinned(X.astype(np.float64)).tobytes()
+        for _ in range(20):
+            det.predict_raw(req)
+        ts = []
+        for _ in range(200):
+            t0 = time.perf_counter()
+            det.predict_raw(req)
+            ts.append(time.perf_counter() - t0)
+        ts.sort()
+        out["rows_%d" % rows] = {"p50_us": ts[100] * 1e6, "p99_us": ts[197] * 1e6, "request_bytes": len(req)}
+    out["note"] = "bytes in (pageable) -> bytes out, one request at a time, state updated per request like the reference"
+    return out
+
+
 def guarded(fn, *a):
     import torch
 
@@ -641,6 +668,7 @@ def main():
         if rank == 0:
             blocks["c4"] = guarded(block_c4, dev)
             blocks["codec"] = guarded(block_codec, dev, hbm)
+            blocks["latency"] = guarded(block_latency, dev)
         if distributed:
             barrier()
 

@@ -119,26 +119,19 @@ sub_scan_totals(const double* __restrict__ subproj, int nsub, int KQ, double* __
   }
 }
 
-// exclusive scan over the chunk totals, in place, starting from this rank's offset (one block, a thread per component)
+// Every chunk forms its own exclusive prefix - the rank offset plus the totals of the chunks before it, added in chunk
+// order (the same sequence of additions in every CTA, so the prefixes are those of one running sum) - and rewrites its
+// 32 rows.  The totals are a few hundred rows of KQ doubles that stay in L2; reading them again per chunk is cheaper
+// than the single-CTA scan kernel that used to sit between the two (77 us cold on the critical path of every batch).
 __global__ void __launch_bounds__(1024)
-sub_scan_chunks(double* __restrict__ chunk_tot, int nchunk, int KQ, const double* __restrict__ rank_off) {
-  for (int comp = threadIdx.x; comp < KQ; comp += blockDim.x) {
-    double run = rank_off[comp];
-#pragma unroll 8
-    for (int c = 0; c < nchunk; ++c) {
-      const double v = chunk_tot[(size_t)c * KQ + comp];
-      chunk_tot[(size_t)c * KQ + comp] = run;
-      run += v;
-    }
-  }
-}
-
-__global__ void __launch_bounds__(1024)
-sub_scan_apply(double* __restrict__ subproj, int nsub, int KQ, const double* __restrict__ chunk_pre) {
+sub_scan_apply(double* __restrict__ subproj, int nsub, int KQ, const double* __restrict__ chunk_tot,
+               const double* __restrict__ rank_off) {
   const int chunk = blockIdx.x, nchunk = gridDim.x;
   const int s0 = chunk * kScanChunk, s1 = min(nsub, s0 + kScanChunk);
   for (int comp = threadIdx.x; comp < KQ; comp += blockDim.x) {
-    double run = chunk_pre[(size_t)chunk * KQ + comp];
+    double run = rank_off[comp];
+#pragma unroll 8
+    for (int c = 0; c < chunk; ++c) run += chunk_tot[(size_t)c * KQ + comp];
     for (int s = s0; s < s1; ++s) {
       const double v = subproj[(size_t)s * KQ + comp];
       subproj[(size_t)s * KQ + comp] = run;
@@ -1562,9 +1555,7 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
   const int nchunk = (int)ceil_div(nsub, kScanChunk);
   sub_scan_totals<<<nchunk, scan_threads(KQ), 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
   SB_LAUNCH_CHECK();
-  sub_scan_chunks<<<1, scan_threads(KQ), 0, st>>>(ws.chunk_tot, nchunk, KQ, rank_proj);
-  SB_LAUNCH_CHECK();
-  sub_scan_apply<<<nchunk, scan_threads(KQ), 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
+  sub_scan_apply<<<nchunk, scan_threads(KQ), 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot, rank_proj);
   SB_LAUNCH_CHECK();
   sub_start<KP><<<(int)ceil_div(nsub, 4), 128, 0, st>>>(ws.subproj, h->d_PC0, h->lay, h->k, (long long)h->n_eff,
                                                        (long long)h->row0, ws.sub_P, ws.sub_Z, ws.sub_flags);
@@ -1617,9 +1608,7 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
     const int nchunk = (int)ceil_div(nsub, kScanChunk);
     sub_scan_totals<<<nchunk, scan_threads(KQ), 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
     SB_LAUNCH_CHECK();
-    sub_scan_chunks<<<1, scan_threads(KQ), 0, st>>>(ws.chunk_tot, nchunk, KQ, ws.rank_proj);
-    SB_LAUNCH_CHECK();
-    sub_scan_apply<<<nchunk, scan_threads(KQ), 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot);
+    sub_scan_apply<<<nchunk, scan_threads(KQ), 0, st>>>(ws.subproj, nsub, KQ, ws.chunk_tot, ws.rank_proj);
     SB_LAUNCH_CHECK();
     sub_start<KP><<<(int)ceil_div(nsub, 4), 128, 0, st>>>(ws.subproj, h->d_PC0, L, h->k, (long long)h->n_eff,
                                                          (long long)h->row0, ws.sub_P, ws.sub_Z, ws.sub_flags);
