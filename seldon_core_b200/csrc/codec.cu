@@ -716,14 +716,14 @@ extern "C" int32_t sb_unpack_listvalue(const uint8_t* d_wire, uint64_t nbytes, i
   const int R = staged_rows(rb);
   if (R > 0 && ((uintptr_t)d_wire & 15) == 0 && cols < (1 << 20)) {
     const size_t smem = (size_t)R * rb + 64;
-    SB_CUDA(cudaFuncSetAttribute(unpack_listvalue_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    SB_CUDA(sb::func_attr_cached(unpack_listvalue_staged, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     int64_t nch = sb::ceil_div(rows, R);
     int grid = (int)(nch < (int64_t)sb::kNumSMs * 12 ? nch : (int64_t)sb::kNumSMs * 12);
     const int RR = cols % 4 == 0 ? ring_rows(rb, kLvStages) : 0;
     if (RR > 0) {
       const int sb = ring_slot_bytes(rb, RR);
       const size_t rsm = (size_t)kLvStages * sb;
-      SB_CUDA(cudaFuncSetAttribute(unpack_listvalue_ring4, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      SB_CUDA(sb::func_attr_cached(unpack_listvalue_ring4, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       const int64_t nch2 = sb::ceil_div(rows, RR);
       const int per_sm = (int)(200 * 1024 / (rsm + 1024)) < 8 ? (int)(200 * 1024 / (rsm + 1024)) : 8;
       const int64_t gmax = (int64_t)sb::kNumSMs * (per_sm > 0 ? per_sm : 1);
@@ -731,7 +731,7 @@ extern "C" int32_t sb_unpack_listvalue(const uint8_t* d_wire, uint64_t nbytes, i
                                                                               (uint32_t)l1, (uint32_t)l2, RR, sb, d_out,
                                                                               ld, d_status);
     } else if (cols % 4 == 0) {
-      SB_CUDA(cudaFuncSetAttribute(unpack_listvalue_staged4, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      SB_CUDA(sb::func_attr_cached(unpack_listvalue_staged4, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       unpack_listvalue_staged4<<<grid, 256, smem, st>>>(d_wire, rows, (int)cols, (int)rb, hdr, (uint32_t)l1, (uint32_t)l2,
                                                        R, d_out, ld, d_status);
     } else {
@@ -795,28 +795,28 @@ extern "C" int32_t sb_pack_listvalue(const void* d_in, int32_t in_dtype, int64_t
       const int64_t gmax = (int64_t)sb::kNumSMs * (per_sm > 0 ? per_sm : 1);
       const int g3 = (int)(nch2 < gmax ? nch2 : gmax);
       if (in_dtype == SB_F32) {
-        SB_CUDA(cudaFuncSetAttribute(pack_listvalue_ring4<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        SB_CUDA(sb::func_attr_cached(pack_listvalue_ring4<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         pack_listvalue_ring4<float><<<g3, 256, rsm, st>>>((const float*)d_in, rows, (int)cols, (int)rb, hdr, (uint32_t)l1,
                                                          (uint32_t)l2, RR, sb, d_wire);
       } else {
-        SB_CUDA(cudaFuncSetAttribute(pack_listvalue_ring4<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        SB_CUDA(sb::func_attr_cached(pack_listvalue_ring4<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         pack_listvalue_ring4<int32_t><<<g3, 256, rsm, st>>>((const int32_t*)d_in, rows, (int)cols, (int)rb, hdr,
                                                            (uint32_t)l1, (uint32_t)l2, RR, sb, d_wire);
       }
     } else if (cols > 0 && cols % 4 == 0 && in_dtype == SB_F32) {
-      SB_CUDA(cudaFuncSetAttribute(pack_listvalue_staged4<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      SB_CUDA(sb::func_attr_cached(pack_listvalue_staged4<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       pack_listvalue_staged4<float><<<g2, 256, smem, st>>>((const float*)d_in, rows, (int)cols, (int)rb, hdr, (uint32_t)l1,
                                                           (uint32_t)l2, R, d_wire);
     } else if (cols > 0 && cols % 4 == 0) {
-      SB_CUDA(cudaFuncSetAttribute(pack_listvalue_staged4<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      SB_CUDA(sb::func_attr_cached(pack_listvalue_staged4<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       pack_listvalue_staged4<int32_t><<<g2, 256, smem, st>>>((const int32_t*)d_in, rows, (int)cols, (int)rb, hdr,
                                                             (uint32_t)l1, (uint32_t)l2, R, d_wire);
     } else if (in_dtype == SB_F32) {
-      SB_CUDA(cudaFuncSetAttribute(pack_listvalue_staged<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      SB_CUDA(sb::func_attr_cached(pack_listvalue_staged<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       pack_listvalue_staged<float><<<g2, 256, smem, st>>>((const float*)d_in, rows, (int)cols, (int)rb, hdr, (uint32_t)l1,
                                                          (uint32_t)l2, R, d_wire);
     } else {
-      SB_CUDA(cudaFuncSetAttribute(pack_listvalue_staged<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      SB_CUDA(sb::func_attr_cached(pack_listvalue_staged<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       pack_listvalue_staged<int32_t><<<g2, 256, smem, st>>>((const int32_t*)d_in, rows, (int)cols, (int)rb, hdr,
                                                            (uint32_t)l1, (uint32_t)l2, R, d_wire);
     }

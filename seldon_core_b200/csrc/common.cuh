@@ -11,6 +11,13 @@ namespace sb {
 
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
+// cudaFuncSetAttribute, remembered per (device, kernel, attribute): the runtime call costs a few microseconds and the
+// launchers used to make it in front of every launch - a visible part of the host time of a small request
+cudaError_t func_attr_cached_impl(const void* fn, cudaFuncAttribute attr, int value);
+template <class T>
+inline cudaError_t func_attr_cached(T* fn, cudaFuncAttribute attr, int value) {
+  return func_attr_cached_impl(reinterpret_cast<const void*>(fn), attr, value);
+}
 
 #define SB_CUDA(call)                                                                              \
   do {                                                                                             \

@@ -616,7 +616,7 @@ int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
   if (h->profile) cudaEventRecord(h->ev[2], st);
   if (d == 64 && !h->force_generic) {
     const size_t sm64 = (size_t)(64 * 128 + 64 * 64) * sizeof(double);  // columns (W | V) + the staged covariance
-    SB_CUDA(cudaFuncSetAttribute(jacobi64_regs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm64));
+    SB_CUDA(sb::func_attr_cached(jacobi64_regs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm64));
     jacobi64_regs<<<1, 512, sm64, st>>>(h->d_C1, h->k, h->KP, h->d_V, h->d_Vf, h->d_evals, h->d_gate, h->d_Vfull, warm);
   } else if ((d == 128 || d == 256) && !h->force_generic) {
     // batches after the first: warm-started block subspace iteration on one CTA; the Jacobi solver below runs only
@@ -645,8 +645,8 @@ int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
     auto launch = [&](auto kernel, int ncta) -> cudaError_t {
       const int spc = (d / 2) / ncta;
       const size_t smc = (size_t)(2 * spc + 1) * 2 * d * sizeof(double);
-      cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc);
-      if (e == cudaSuccess && ncta > 8) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+      cudaError_t e = sb::func_attr_cached(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc);
+      if (e == cudaSuccess && ncta > 8) e = sb::func_attr_cached(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
       if (e != cudaSuccess) return e;
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3(ncta);
@@ -680,7 +680,7 @@ int launch_eigh(sb_maha* h, const MahaWs& ws, cudaStream_t st) {
       h->sub_state = 2;
     }
   } else if (need <= 200 * 1024) {
-    SB_CUDA(cudaFuncSetAttribute(jacobi_topk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    SB_CUDA(sb::func_attr_cached(jacobi_topk<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     jacobi_topk<true><<<1, 1024, need, st>>>(h->d_C1, d, h->k, h->KP, nullptr, nullptr, h->d_V, h->d_Vf, h->d_evals,
                                             h->d_gate, h->d_Vfull, warm);
   } else {

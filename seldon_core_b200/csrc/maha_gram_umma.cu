@@ -540,7 +540,7 @@ int launch_umma_d(const sb_maha* h, const float* X, int64_t ld, const MahaWs& ws
 #define SB_UMMA_LAUNCH2(CLIPV, TERMSV, STDV)                                                                            \
   do {                                                                                                                  \
     const size_t smem = umma_smem_bytes(D, TERMSV);                                                                     \
-    SB_CUDA(cudaFuncSetAttribute(pass1_gram_umma<D, CLIPV, TERMSV, STDV>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+    SB_CUDA(sb::func_attr_cached(pass1_gram_umma<D, CLIPV, TERMSV, STDV>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                  (int)smem));                                                                           \
     pass1_gram_umma<D, CLIPV, TERMSV, STDV><<<grid, umma_block(D), smem, st>>>(                                         \
         X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_in_mu, h->d_in_is, ws.partials);                              \

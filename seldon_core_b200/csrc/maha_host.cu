@@ -325,7 +325,7 @@ extern "C" int32_t sb_maha_get_state(sb_maha_t* h, double* h_mean, double* h_C, 
   if (h_C) SB_CUDA(cudaMemcpyAsync(h_C, h->d_C, d * d * sizeof(double), cudaMemcpyDeviceToHost, st));
   if (h_clip_lo) SB_CUDA(cudaMemcpyAsync(h_clip_lo, h->d_lo, d * sizeof(double), cudaMemcpyDeviceToHost, st));
   if (h_clip_hi) SB_CUDA(cudaMemcpyAsync(h_clip_hi, h->d_hi, d * sizeof(double), cudaMemcpyDeviceToHost, st));
-  SB_CUDA(cudaStreamSynchronize(st));
+  if (h_mean || h_C || h_clip_lo || h_clip_hi) SB_CUDA(cudaStreamSynchronize(st));  // the scalars are host mirrors
   if (n) *n = h->n;
   if (has_state) *has_state = h->has_state;
   if (has_clip) *has_clip = h->has_clip;

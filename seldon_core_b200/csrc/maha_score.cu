@@ -1532,7 +1532,7 @@ int launch_prefix_kp(sb_maha* h, const MahaWs& ws, double* rank_proj, cudaStream
   if (h->profile) cudaEventRecord(h->ev[4], st);
   const int stage_v = (size_t)2 * d * KP * sizeof(double) <= 200 * 1024;
   const size_t pc_smem = (size_t)(stage_v ? 2 : 1) * d * KP * sizeof(double);
-  SB_CUDA(cudaFuncSetAttribute(project_cov, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  SB_CUDA(sb::func_attr_cached(project_cov, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   project_cov<<<1, 1024, pc_smem, st>>>(h->d_C, h->d_V, d, KP, h->d_PC0, stage_v);
   SB_LAUNCH_CHECK();
   int grid = nsub < kNumSMs * 8 ? nsub : kNumSMs * 8;
@@ -1585,7 +1585,7 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
 #define SB_LAUNCH_PROJECT2(NB, CLIPV, STDV)                                                                         \
     do {                                                                                                           \
       const size_t psm = proj_smem_bytes(NB, CLIPV);                                                               \
-      SB_CUDA(cudaFuncSetAttribute(project_rows<NB, CLIPV, STDV>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
+      SB_CUDA(sb::func_attr_cached(project_rows<NB, CLIPV, STDV>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
                                    (int)psm));                                                                     \
       project_rows<NB, CLIPV, STDV><<<pgrid, 128, psm, st>>>(X, ld, L, h->d_mean_f, h->d_lo_f, h->d_hi_f,          \
                                                             h->d_in_mu, h->d_in_is, h->d_Vf, ws.proj_Z, ws.proj_D, \
@@ -1642,7 +1642,7 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
       if (cgrid > kNumSMs * kChain4Ctas) cgrid = kNumSMs * kChain4Ctas;
       if (h->use_clip) {
         const size_t csm = (size_t)(NCH * ES + NCH * CS + 2 * NCH * ES) * sizeof(float);
-        SB_CUDA(cudaFuncSetAttribute(chain4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csm));
+        SB_CUDA(sb::func_attr_cached(chain4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csm));
         chain4<true><<<cgrid, 32 * kChain4Warps, csm, st>>>(ws.proj_Z, ws.proj_D, ws.proj_flag, L, ws.sub_P, ws.sub_Z,
                                                            ws.sub_flags, (long long)h->n_eff, (long long)h->row0,
                                                            h->threshold, h->d_gate, h->d_score_sum, score, flag);
@@ -1672,12 +1672,12 @@ int launch_score_kp(sb_maha* h, const float* X, int64_t ld, float* score, int32_
     if (grid > kNumSMs * 4) grid = kNumSMs * 4;
     size_t smem = ((size_t)d * KP + 3 * (size_t)d + 4 + (size_t)groups_per_cta * 3 * KP) * sizeof(float);
     if (h->use_clip) {
-      SB_CUDA(cudaFuncSetAttribute(score_chain<KP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      SB_CUDA(sb::func_attr_cached(score_chain<KP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
       score_chain<KP, true><<<grid, 128, smem, st>>>(X, ld, d, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf, ws.sub_P,
                                                     ws.sub_Z, ws.sub_flags, (long long)h->n_eff, (long long)h->row0,
                                                     h->threshold, h->d_gate, h->d_score_sum, score, flag);
     } else {
-      SB_CUDA(cudaFuncSetAttribute(score_chain<KP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      SB_CUDA(sb::func_attr_cached(score_chain<KP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
       score_chain<KP, false><<<grid, 128, smem, st>>>(X, ld, d, L, h->d_mean_f, h->d_lo_f, h->d_hi_f, h->d_Vf,
                                                      ws.sub_P, ws.sub_Z, ws.sub_flags, (long long)h->n_eff,
                                                      (long long)h->row0, h->threshold, h->d_gate, h->d_score_sum,

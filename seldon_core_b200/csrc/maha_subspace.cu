@@ -415,11 +415,11 @@ int launch_subspace(sb_maha* h, int* conv_flag, cudaStream_t st) {
   const size_t smem = ((size_t)2 * d * kLD + 3 * kB * kLS + 2 * kB + 32 + 2 * kCR * d) * sizeof(double);
   int* ortho = reinterpret_cast<int*>(h->d_gate + 46);
   if (d == 256) {
-    SB_CUDA(cudaFuncSetAttribute(subspace_topk<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SB_CUDA(sb::func_attr_cached(subspace_topk<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     subspace_topk<256><<<1, kNT, smem, st>>>(h->d_C1, h->k, h->KP, h->d_Vsub, h->d_V, h->d_Vf, h->d_evals, h->d_gate,
                                              conv_flag, ortho, 8, 1e-5);
   } else {
-    SB_CUDA(cudaFuncSetAttribute(subspace_topk<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SB_CUDA(sb::func_attr_cached(subspace_topk<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     subspace_topk<128><<<1, kNT, smem, st>>>(h->d_C1, h->k, h->KP, h->d_Vsub, h->d_V, h->d_Vf, h->d_evals, h->d_gate,
                                              conv_flag, ortho, 8, 1e-5);
   }

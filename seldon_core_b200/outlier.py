@@ -64,13 +64,14 @@ class OutlierMahalanobisB200(object):
         with self._lock:
             nrows, n_flagged, score_sum = self._last_sums()
             self.nb_outliers += n_flagged
+            n = self.n
             g = lambda key, value: {"type": "GAUGE", "key": key, "value": value}
             return [
                 g("is_outlier", n_flagged / nrows),
                 g("outlier_score", score_sum / nrows),
                 g("nb_outliers", int(self.nb_outliers)),
-                g("fraction_outliers", int(self.nb_outliers) / self.n),
-                g("observation", self.n),
+                g("fraction_outliers", int(self.nb_outliers) / n),
+                g("observation", n),
                 g("threshold", self.threshold),
             ]
 
@@ -219,7 +220,16 @@ class OutlierMahalanobisB200(object):
     def n(self):
         if self._h is None:
             return self._restore["n"] if self._restore else 0
-        return self._state()["n"]
+        if getattr(self, "_cached_state", None) is not None:
+            return self._cached_state["n"]
+        # the row count is mirrored on the host: no need to bring mean, C and the clip bounds back for it
+        import torch
+
+        n, hs, hc = ctypes.c_int64(), ctypes.c_int32(), ctypes.c_int32()
+        with torch.cuda.device(self._device):
+            _cabi.check(_cabi.lib().sb_maha_get_state(self._h, None, None, None, None, ctypes.byref(n), ctypes.byref(hs),
+                                                      ctypes.byref(hc), torch.cuda.current_stream().cuda_stream))
+        return n.value
 
     @property
     def mean(self):
