@@ -337,11 +337,11 @@ def block_c5(dev, hbm, rank, world, tf32):
             dist.barrier()
             torch.cuda.synchronize()
 
-    for _ in range(3):
+    for _ in range(5):
         s, f, _ = batch()
     barrier()
     mism = int((f.to(torch.int8) != labels).sum().item())
-    nb = 5
+    nb = 20
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
