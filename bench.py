@@ -568,7 +568,8 @@ def main():
     from seldon_core_b200 import dist as sdist
 
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU fallback)"
-    assert args.warmup >= 3, "timing rules: at least 3 warm-up steps"
+    if args.warmup < 3:
+        args.warmup = 3  # timing rules: at least 3 warm-up steps (the printed line carries the value used)
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     distributed = world > 1

@@ -94,10 +94,19 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 // three 32 KB slots in flight per SM cost no registers) and the tile ring gives up one slot for that.
 __host__ __device__ constexpr bool umma_raw_staged(int D) { return D == 64 || D == 256; }  // measured: d = 128 is faster without
 __host__ __device__ constexpr int umma_tile_stages(int D) { return umma_raw_staged(D) ? 2 : 3; }
-constexpr int kRawStagesMax = 3;
-__host__ __device__ constexpr int umma_raw_stages(int D) { return D == 64 ? 3 : 2; }  // d = 256 has 5 KB of constants more
+constexpr int kRawStagesMax = 8;
+__host__ __device__ constexpr int umma_raw_stages(int D) { return D == 64 ? SB_P1_RAW64 : 2; }  // d = 256 has 5 KB of constants more
 // rows per chunk: 8192 / D, so every tile is 32 KB and every thread converts four float4 per chunk
-__host__ __device__ constexpr int umma_chunk_rows(int D) { return 8192 / D; }
+// d = 64: rows per chunk and raw-ring depth.  Measured (16 Mi rows, round 2): 128 rows / 3 slots 0.94 ms; 64 rows with
+// 6 or 8 slots (more, smaller copies in flight) 1.12 / 1.15 ms - the per-chunk barrier traffic costs more than the
+// deeper ring gives.
+#ifndef SB_P1_ROWS64
+#define SB_P1_ROWS64 128
+#endif
+#ifndef SB_P1_RAW64
+#define SB_P1_RAW64 3
+#endif
+__host__ __device__ constexpr int umma_chunk_rows(int D) { return D == 64 ? SB_P1_ROWS64 : 8192 / D; }
 
 __host__ __device__ constexpr size_t umma_smem_bytes(int D, int terms) {
   return (size_t)umma_tile_stages(D) * (terms == 3 ? 2 : 1) * umma_chunk_rows(D) * D * 4 +
