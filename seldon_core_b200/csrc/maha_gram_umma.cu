@@ -90,13 +90,6 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
       : "memory");
 }
 
-// d = 64 is HBM-latency bound: its rows are staged raw in shared memory by bulk copies (cp.async.bulk, a loader warp;
-// three 32 KB slots in flight per SM cost no registers) and the tile ring gives up one slot for that.
-__host__ __device__ constexpr bool umma_raw_staged(int D) { return D == 64 || D == 256; }  // measured: d = 128 is faster without
-__host__ __device__ constexpr int umma_tile_stages(int D) { return umma_raw_staged(D) ? 2 : 3; }
-constexpr int kRawStagesMax = 8;
-__host__ __device__ constexpr int umma_raw_stages(int D) { return D == 64 ? SB_P1_RAW64 : 2; }  // d = 256 has 5 KB of constants more
-// rows per chunk: 8192 / D, so every tile is 32 KB and every thread converts four float4 per chunk
 // d = 64: rows per chunk and raw-ring depth.  Measured (16 Mi rows, round 2): 128 rows / 3 slots 0.94 ms; 64 rows with
 // 6 or 8 slots (more, smaller copies in flight) 1.12 / 1.15 ms - the per-chunk barrier traffic costs more than the
 // deeper ring gives.
@@ -106,6 +99,13 @@ __host__ __device__ constexpr int umma_raw_stages(int D) { return D == 64 ? SB_P
 #ifndef SB_P1_RAW64
 #define SB_P1_RAW64 3
 #endif
+// d = 64 is HBM-latency bound: its rows are staged raw in shared memory by bulk copies (cp.async.bulk, a loader warp;
+// three 32 KB slots in flight per SM cost no registers) and the tile ring gives up one slot for that.
+__host__ __device__ constexpr bool umma_raw_staged(int D) { return D == 64 || D == 256; }  // measured: d = 128 is faster without
+__host__ __device__ constexpr int umma_tile_stages(int D) { return umma_raw_staged(D) ? 2 : 3; }
+constexpr int kRawStagesMax = 8;
+__host__ __device__ constexpr int umma_raw_stages(int D) { return D == 64 ? SB_P1_RAW64 : 2; }  // d = 256 has 5 KB of constants more
+// rows per chunk: 8192 / D, so every tile is 32 KB and every thread converts four float4 per chunk
 __host__ __device__ constexpr int umma_chunk_rows(int D) { return D == 64 ? SB_P1_ROWS64 : 8192 / D; }
 
 __host__ __device__ constexpr size_t umma_smem_bytes(int D, int terms) {
