@@ -139,3 +139,16 @@ def test_graph_rejects_bad_routing():
     g = GraphB200(Unit("r", "ROUTER", BadRouter(), [Unit("m", "MODEL", DeviceModel(np.eye(4), "m"))]))
     with pytest.raises(SeldonB200Error, match="Invalid branch index"):
         g.predict(torch.zeros((2, 4), device="cuda"))
+
+
+def test_random_abtest_against_the_committed_stream():
+    """Decisions of the kernel against tests/golden/java_random_1337.npz (the first 1 000 nextFloat() values of
+    java.util.Random(1337)) for several ratios: branch 0 iff nextFloat() <= ratioA (RandomABTestUnit.java:52)."""
+    import os
+
+    from conftest import GOLDEN
+
+    f = np.load(os.path.join(GOLDEN, "java_random_1337.npz"))["next_float"]
+    for ratio in (0.0, 0.1, 0.5, 0.9, 1.0, float(f[10])):
+        dec = RandomABTestB200(ratioA=ratio).run_batched(1000).cpu().numpy()
+        assert np.array_equal(dec, (f > np.float32(ratio)).astype(np.int32)), ratio
