@@ -74,6 +74,12 @@ else:
     for _ in range(3):
         _cabi.check(L.sb_json_ndarray_count(buf.data_ptr(), len(text), ws.data_ptr(), ws.numel() * 8, counts.data_ptr(), st))
         _cabi.check(L.sb_unpack_json_ndarray(buf.data_ptr(), len(text), rows, cols, ws.data_ptr(), y.data_ptr(), cols, status.data_ptr(), st))
+    from seldon_core_b200 import RandomABTestB200, codec  # noqa: E402
+
+    xe = torch.randn((1 << 18, cols), device=dev)
+    for _ in range(3):
+        codec.encode_json_ndarray_device(xe)
+    RandomABTestB200(ratioA=0.5).run_batched(1 << 24)
     kids = [torch.softmax(torch.randn((1 << 18, 1000), device=dev), dim=1) for _ in range(8)]
     for _ in range(3):
         MeanCombinerB200.aggregate_device(kids)
