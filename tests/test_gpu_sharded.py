@@ -58,3 +58,28 @@ def test_uneven_shards_against_the_oracle(d, bounds):
     p2 = ref.predict(X2.astype(np.float64), None)
     for det in (dets[0], dets[-2]):
         assert np.array_equal(det.predict(X2, None), p2) and rel_err(det.score, ref.score).max() < TOL
+
+
+def test_cold_start_batch_split_over_ranks():
+    """The FIRST request batch of a deployment, split over three ranks (no priming): rank 0 finds the warm-up gate in its
+    rows, the later ranks start from the projected prefix of the ranks before them and are open from their first row -
+    scores equal to the oracle's single call (the rows right after the gate opening at the cold-start tolerance)."""
+    import torch
+
+    k, d = 16, 64
+    bounds = [0, 20000, 20001, 70000]
+    X, _ = synth.maha_rows_numpy(bounds[-1], d, k, seed=64)
+    ref = MahalanobisLean(n_components=k)
+    pr = ref.predict(X.astype(np.float64), None)
+    dets = [OutlierMahalanobisB200(n_components=k) for _ in range(len(bounds) - 1)]
+    sg, pg = run_sharded(dets, torch.from_numpy(X).cuda(), bounds, d)
+    first_open = int(np.flatnonzero(ref.score)[0])
+    settle = first_open + 12 * k
+    assert np.all(sg[:first_open] == 0.0)
+    err = rel_err(sg, ref.score)
+    assert err[first_open:settle].max() < 5e-2 and err[settle:].max() < TOL
+    safe = np.abs(ref.score - 25.0) > 2 * TOL * 25.0
+    safe[first_open:settle] &= np.abs(ref.score[first_open:settle] - 25.0) > 2.5
+    assert np.array_equal(pg[safe], pr[safe])
+    for det in dets:
+        assert det.n == ref.n and norm_err(det.C, ref.C) < TOL
